@@ -1,0 +1,258 @@
+"""ctypes bindings for the TEST-ONLY oracles under oracle/.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import
+this module.  The product package (laser_slam_b200) never does.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = os.path.join(_HERE, "_build", "liboracle.so")
+_REF = os.path.join(_HERE, "_ref", "libzhpsm_ref.so")
+
+
+def build(quiet=True):
+    """Compile oracle/_build/liboracle.so and (when /root/reference exists) oracle/_ref/libzhpsm_ref.so."""
+    subprocess.run(["make", "-C", _HERE, "all"], check=True,
+                   stdout=subprocess.DEVNULL if quiet else None)
+
+
+class SmParams(C.Structure):
+    _fields_ = [
+        ("laser_ref", C.c_void_p), ("laser_sens", C.c_void_p),
+        ("first_guess", C.c_double * 3),
+        ("max_angular_correction_deg", C.c_double), ("max_linear_correction", C.c_double),
+        ("max_iterations", C.c_int), ("epsilon_xy", C.c_double), ("epsilon_theta", C.c_double),
+        ("max_correspondence_dist", C.c_double), ("sigma", C.c_double),
+        ("use_corr_tricks", C.c_int), ("restart", C.c_int),
+        ("restart_threshold_mean_error", C.c_double), ("restart_dt", C.c_double),
+        ("restart_dtheta", C.c_double), ("clustering_threshold", C.c_double),
+        ("orientation_neighbourhood", C.c_int), ("use_point_to_line_distance", C.c_int),
+        ("do_alpha_test", C.c_int), ("do_alpha_test_thresholdDeg", C.c_double),
+        ("outliers_maxPerc", C.c_double), ("outliers_adaptive_order", C.c_double),
+        ("outliers_adaptive_mult", C.c_double), ("do_visibility_test", C.c_int),
+        ("outliers_remove_doubles", C.c_int), ("do_compute_covariance", C.c_int),
+        ("debug_verify_tricks", C.c_int), ("use_ml_weights", C.c_int), ("use_sigma_weights", C.c_int),
+        ("min_reading", C.c_double), ("max_reading", C.c_double),
+    ]
+
+
+class SmResult(C.Structure):
+    _fields_ = [
+        ("valid", C.c_int), ("x", C.c_double * 3), ("iterations", C.c_int), ("nvalid", C.c_int),
+        ("error", C.c_double), ("cov_x_m", C.c_double * 9), ("corr_hash", C.c_uint), ("n_loops", C.c_int),
+    ]
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB):
+            build()
+        _lib = C.CDLL(_LIB)
+        _lib.orc_sm_default_params.argtypes = [C.POINTER(SmParams), C.c_int, C.c_int]
+        _lib.orc_median_filter.argtypes = [C.c_void_p, C.c_int]
+        _lib.orc_zhcsm_fmatch.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int,
+                                          C.POINTER(SmParams), C.c_void_p, C.c_void_p, C.POINTER(SmResult),
+                                          C.c_void_p, C.c_void_p]
+        _lib.orc_zhcsm_fmatch.restype = C.c_int
+        _lib.orc_zhcsm_fmatch_batch.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_float,
+                                                C.c_float, C.c_int, C.c_int, C.POINTER(SmParams), C.c_void_p,
+                                                C.c_void_p, C.c_int]
+        _lib.orc_poly_greatest_real_root.argtypes = [C.c_void_p, C.c_void_p]
+        _lib.orc_poly_greatest_real_root.restype = C.c_int
+    return _lib
+
+
+RESULT_DTYPE = np.dtype([("valid", "i4"), ("_p0", "i4"), ("x", "f8", 3), ("iterations", "i4"), ("nvalid", "i4"),
+                         ("error", "f8"), ("cov", "f8", 9), ("corr_hash", "u4"), ("n_loops", "i4")])
+assert RESULT_DTYPE.itemsize == C.sizeof(SmResult), (RESULT_DTYPE.itemsize, C.sizeof(SmResult))
+
+
+def default_params(min_range_cm=10, max_range_cm=5000, **over):
+    p = SmParams()
+    lib().orc_sm_default_params(C.byref(p), int(min_range_cm), int(max_range_cm))
+    for k, v in over.items():
+        setattr(p, k, v)
+    return p
+
+
+def median_filter(r):
+    """In-place 5-tap median of a float32 vector (returns a filtered copy)."""
+    out = np.ascontiguousarray(r, dtype=np.float32).copy()
+    lib().orc_median_filter(out.ctypes.data, out.size)
+    return out
+
+
+def zhcsm_fmatch(ref_r_cm, sens_r_cm, fi_min, dfi, min_range_cm, max_range_cm, params=None, first_guess=None,
+                 want_corr=False):
+    """CCanonicalMatcher::FMatch on already median-filtered float32 cm ranges."""
+    ref = np.ascontiguousarray(ref_r_cm, dtype=np.float32)
+    sens = np.ascontiguousarray(sens_r_cm, dtype=np.float32)
+    n = ref.size
+    pose = np.zeros(3, np.float32)
+    res = SmResult()
+    j1 = np.full(n, -1, np.int32)
+    j2 = np.full(n, -1, np.int32)
+    fg = None if first_guess is None else np.ascontiguousarray(first_guess, dtype=np.float64)
+    ret = lib().orc_zhcsm_fmatch(ref.ctypes.data, sens.ctypes.data, n, np.float32(fi_min), np.float32(dfi),
+                                 int(min_range_cm), int(max_range_cm),
+                                 C.byref(params) if params is not None else None,
+                                 None if fg is None else fg.ctypes.data, pose.ctypes.data, C.byref(res),
+                                 j1.ctypes.data if want_corr else None, j2.ctypes.data if want_corr else None)
+    out = dict(ret=ret, pose_cm=pose, valid=res.valid, x=np.array(res.x[:]), iterations=res.iterations,
+               nvalid=res.nvalid, error=res.error, cov=np.array(res.cov_x_m[:]).reshape(3, 3),
+               corr_hash=res.corr_hash, n_loops=res.n_loops)
+    if want_corr:
+        out["j1"], out["j2"] = j1, j2
+    return out
+
+
+def zhcsm_fmatch_batch(scans_cm, ref_idx, sens_idx, fi_min, dfi, min_range_cm, max_range_cm, params=None,
+                       first_guess=None, nthreads=1):
+    scans = np.ascontiguousarray(scans_cm, dtype=np.float32)
+    ri = np.ascontiguousarray(ref_idx, dtype=np.int32)
+    si = np.ascontiguousarray(sens_idx, dtype=np.int32)
+    out = np.zeros(ri.size, RESULT_DTYPE)
+    fg = None if first_guess is None else np.ascontiguousarray(first_guess, dtype=np.float64)
+    lib().orc_zhcsm_fmatch_batch(scans.ctypes.data, scans.shape[1], ri.ctypes.data, si.ctypes.data, ri.size,
+                                 np.float32(fi_min), np.float32(dfi), int(min_range_cm), int(max_range_cm),
+                                 C.byref(params) if params is not None else None,
+                                 None if fg is None else fg.ctypes.data, out.ctypes.data, int(nthreads))
+    return out
+
+
+# ---------------------------------------------------------------------------------------------
+# oracle/_ref/libzhpsm_ref.so: the reference's own zhpsm sources compiled by oracle/Makefile
+# ---------------------------------------------------------------------------------------------
+_ref = None
+
+
+def have_ref():
+    return os.path.exists(_REF)
+
+
+def ref():
+    global _ref
+    if _ref is None:
+        if not os.path.exists(_REF):
+            raise RuntimeError("oracle/_ref/libzhpsm_ref.so is absent (build it where /root/reference exists: "
+                               "make -C oracle ref)")
+        _ref = C.CDLL(_REF)
+        _ref.zhpsm_ref_create.restype = C.c_void_p
+        _ref.zhpsm_ref_create.argtypes = [C.c_char_p, C.c_float, C.c_int]
+        _ref.zhpsm_ref_destroy.argtypes = [C.c_void_p]
+        _ref.zhpsm_ref_params.argtypes = [C.c_void_p] + [C.c_void_p] * 7
+        _ref.zhpsm_ref_tables.argtypes = [C.c_void_p] * 4
+        _ref.zhpsm_ref_preprocess.argtypes = [C.c_void_p] * 4
+        _ref.zhpsm_ref_median.argtypes = [C.c_void_p] * 2
+        _ref.zhpsm_ref_scan_project.argtypes = [C.c_void_p] * 7
+        _ref.zhpsm_ref_match.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 9
+        _ref.zhpsm_ref_match.restype = C.c_int
+        _ref.zhpsm_ref_error_index2.argtypes = [C.c_void_p] * 11
+        _ref.zhpsm_ref_fmatch.argtypes = [C.c_void_p] * 7 + [C.c_int, C.c_void_p, C.c_void_p]
+        _ref.zhpsm_ref_is_corridor.argtypes = [C.c_void_p] * 4
+        _ref.zhpsm_ref_is_corridor.restype = C.c_int
+        _ref.zhpsm_ref_match_batch.argtypes = [C.c_char_p, C.c_float, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                               C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
+                                               C.c_void_p, C.c_int]
+    return _ref
+
+
+class RefPolarMatch:
+    """The reference's CPolarMatch (src/zhpsm/ZHPolar_Match.h:16-88), compiled unmodified."""
+
+    def __init__(self, laser, fi_min=float("nan"), max_range_cm=0):
+        self.laser = laser.encode()
+        self.fi_min_override = float(fi_min)
+        self.max_range_override = int(max_range_cm)
+        self.h = ref().zhpsm_ref_create(self.laser, C.c_float(fi_min), int(max_range_cm))
+        if not self.h:
+            raise ValueError("unknown laser " + laser)
+        n, mn, mx, mv, w = C.c_int(), C.c_int(), C.c_int(), C.c_int(), C.c_int()
+        fi, dfi = C.c_float(), C.c_float()
+        ref().zhpsm_ref_params(self.h, C.byref(n), C.byref(fi), C.byref(dfi), C.byref(mn), C.byref(mx),
+                               C.byref(mv), C.byref(w))
+        self.n, self.fi_min, self.dfi = n.value, np.float32(fi.value), np.float32(dfi.value)
+        self.min_range, self.max_range, self.min_valid, self.window = mn.value, mx.value, mv.value, w.value
+
+    def __del__(self):
+        try:
+            if self.h:
+                ref().zhpsm_ref_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    def tables(self):
+        fi, si, co = (np.zeros(self.n, np.float32) for _ in range(3))
+        ref().zhpsm_ref_tables(self.h, fi.ctypes.data, si.ctypes.data, co.ctypes.data)
+        return fi, si, co
+
+    def preprocess(self, r, bad=None):
+        r = np.ascontiguousarray(r, np.float32).copy()
+        bad = np.zeros(self.n, np.int32) if bad is None else np.ascontiguousarray(bad, np.int32).copy()
+        seg = np.zeros(self.n, np.int32)
+        ref().zhpsm_ref_preprocess(self.h, r.ctypes.data, bad.ctypes.data, seg.ctypes.data)
+        return r, bad, seg
+
+    def median(self, r):
+        r = np.ascontiguousarray(r, np.float32).copy()
+        ref().zhpsm_ref_median(self.h, r.ctypes.data)
+        return r
+
+    def scan_project(self, r, bad, seg, pose):
+        r, bad, seg = _f32(r), _i32(bad), _i32(seg)
+        pose = np.asarray(pose, np.float32)
+        new_r = np.zeros(self.n, np.float32)
+        new_bad = np.zeros(self.n, np.int32)
+        ref().zhpsm_ref_scan_project(self.h, r.ctypes.data, bad.ctypes.data, seg.ctypes.data, pose.ctypes.data,
+                                     new_r.ctypes.data, new_bad.ctypes.data)
+        return new_r, new_bad
+
+    def match(self, algo, ref_scan, act_scan, act_pose=(0, 0, 0), ref_pose=(0, 0, 0)):
+        """algo 0 pm_psm, 1 pm_icp, 2 pm_psm->pm_icp; scans = (r,bad,seg) preprocessed."""
+        rr, rb, rs = _f32(ref_scan[0]), _i32(ref_scan[1]), _i32(ref_scan[2])
+        ar, ab, as_ = _f32(act_scan[0]), _i32(act_scan[1]), _i32(act_scan[2])
+        rp = np.asarray(ref_pose, np.float32)
+        pose = np.asarray(act_pose, np.float32).copy()
+        err = C.c_float()
+        st = ref().zhpsm_ref_match(self.h, int(algo), rr.ctypes.data, rb.ctypes.data, rs.ctypes.data, rp.ctypes.data,
+                                   ar.ctypes.data, ab.ctypes.data, as_.ctypes.data, pose.ctypes.data,
+                                   C.cast(C.byref(err), C.c_void_p))
+        return st, pose, err.value
+
+    def error_index2(self, ref_scan, act_scan, act_pose, ref_pose=(0, 0, 0)):
+        rr, rb, rs = _f32(ref_scan[0]), _i32(ref_scan[1]), _i32(ref_scan[2])
+        ar, ab, as_ = _f32(act_scan[0]), _i32(act_scan[1]), _i32(act_scan[2])
+        rp, ap = np.asarray(ref_pose, np.float32), np.asarray(act_pose, np.float32)
+        out = np.zeros(2, np.float32)
+        assoc = C.c_int()
+        ref().zhpsm_ref_error_index2(self.h, rr.ctypes.data, rb.ctypes.data, rs.ctypes.data, rp.ctypes.data,
+                                     ar.ctypes.data, ab.ctypes.data, as_.ctypes.data, ap.ctypes.data,
+                                     out.ctypes.data, C.cast(C.byref(assoc), C.c_void_p))
+        return out, assoc.value
+
+    def match_batch(self, algo, r, bad, seg, ref_idx, act_idx, nthreads=1):
+        r, bad, seg = _f32(r), _i32(bad), _i32(seg)
+        ri, ai = _i32(ref_idx), _i32(act_idx)
+        poses = np.zeros((ri.size, 3), np.float32)
+        status = np.zeros(ri.size, np.int32)
+        ref().zhpsm_ref_match_batch(self.laser, C.c_float(self.fi_min_override), self.max_range_override, int(algo),
+                                    r.ctypes.data, bad.ctypes.data, seg.ctypes.data, self.n, ri.ctypes.data,
+                                    ai.ctypes.data, ri.size, poses.ctypes.data, status.ctypes.data, int(nthreads))
+        return poses, status
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, np.float32)
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, np.int32)
