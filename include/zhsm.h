@@ -1,0 +1,140 @@
+/*
+ * include/zhsm.h -- C ABI of the B200 batched 2D scan-matching engine (libzhsm.so).
+ *
+ * Drop-in boundary for the reference's three matchers.  Every entry point is
+ * plain C: pointers + sizes, no C++/torch types.  Status codes replace the reference's `throw 1`
+ * (src/zhpsm/ZHPolar_Match.cpp:1095,1106,1239,1831) and `output->valid==0`
+ * (src/zhcsm/ZHCanonical_Matcher.cpp:275-283); nothing aborts a batch.
+ *
+ * Scans live in a "scan pool": [S][n] float32 ranges in cm, row-major, exactly PMScan::r
+ * (src/zhpsm/PolarParameter.h:105-184).  A batch is a list of JOBS (ref scan index, sens scan index,
+ * optional first guess) so consecutive-scan odometry, many-to-one loop-closure candidates and
+ * multi-start share one entry point and each scan is read from HBM once per job.
+ *
+ * There is NO CPU fallback: every compute entry returns ZHSM_ERR_CUDA when no sm_100 device is usable.
+ */
+#ifndef ZHSM_H
+#define ZHSM_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct zhsm_handle zhsm_handle;
+
+typedef enum {
+    ZHSM_OK = 0,
+    ZHSM_ERR_ARG = 1,
+    ZHSM_ERR_CUDA = 2,
+    ZHSM_ERR_NOMEM = 3,
+    ZHSM_ERR_UNSUPPORTED = 4
+} zhsm_status;
+
+/* per-job status in zhsm_result.status */
+enum {
+    ZHSM_JOB_OK = 0,
+    ZHSM_JOB_TOO_FEW_POINTS = 1, /* pm_icp/pm_translation_estimation "not enough points"; icp_loop <5% correspondences */
+    ZHSM_JOB_SINGULAR = 2,       /* determinant too small / gpc_solve failed */
+    ZHSM_JOB_SEARCH_FAILED = 3,  /* pm_orientation_search failed */
+    ZHSM_JOB_INVALID_SCAN = 4    /* ld_valid_fields rejected a scan (sm_icp returns valid=0 before iterating) */
+};
+
+/* POD image of Base_PARAM (src/zhpsm/PolarParameter.h:42-83) */
+typedef struct zhsm_laser {
+    int32_t n;                /* pm_l_points */
+    float fi_min;             /* pm_fi_min [rad] */
+    float dfi;                /* pm_dfi [rad] */
+    int32_t min_range_cm;     /* pm_min_range (PM_MIN_RANGE = 10) */
+    int32_t max_range_cm;     /* pm_max_range */
+    int32_t min_valid_points; /* pm_min_valid_points */
+    int32_t scan_window;      /* pm_scan_window */
+    int32_t reserved;
+} zhsm_laser;
+
+/* The sm_params fields CCanonicalMatcher::sm_init sets (src/zhcsm/ZHCanonical_Matcher.cpp:83-157).
+ * zhsm_plicp_default_params() fills the reference's values. */
+typedef struct zhsm_plicp_params {
+    double max_angular_correction_deg;
+    double max_linear_correction;
+    double epsilon_xy;
+    double epsilon_theta;
+    double max_correspondence_dist;
+    double sigma;
+    double restart_threshold_mean_error;
+    double restart_dt;
+    double restart_dtheta;
+    double outliers_maxPerc;
+    double outliers_adaptive_order;
+    double outliers_adaptive_mult;
+    double min_reading; /* m */
+    double max_reading; /* m */
+    int32_t max_iterations;
+    int32_t use_corr_tricks;          /* only 1 (the reference's setting) is implemented */
+    int32_t restart;
+    int32_t use_point_to_line_distance; /* only 1 */
+    int32_t outliers_remove_doubles;
+    int32_t do_compute_covariance;
+    int32_t reserved[2];
+} zhsm_plicp_params;
+
+/* Fixed 128-byte result record; also the NCCL all-gather record. */
+typedef struct zhsm_result {
+    double x[3];        /* PL-ICP / ICP: m,m,rad.  PSM family: cm,cm,rad (PMScan units) */
+    double cov[6];      /* upper triangle xx xy xt yy yt tt */
+    double error;       /* sm_result.error / returned avg error */
+    int32_t valid;      /* sm_result.valid */
+    int32_t iterations; /* sm_result.iterations (sum over restarts) */
+    int32_t nvalid;     /* sm_result.nvalid */
+    int32_t status;     /* ZHSM_JOB_* */
+    float goodness;
+    float quality;
+    uint32_t corr_hash; /* ld_corr_hash of the final correspondences */
+    int32_t n_loops;    /* icp_loop executions (1 + restarts) */
+    int32_t reserved[4];
+} zhsm_result;
+
+/* flags for batch calls */
+#define ZHSM_SCANS_ON_DEVICE 1u   /* scan pool pointer is device memory */
+#define ZHSM_JOBS_ON_DEVICE 2u    /* ref_idx/sens_idx/first_guess pointers are device memory */
+#define ZHSM_RESULTS_ON_DEVICE 4u /* results (and corr outputs) are device memory */
+#define ZHSM_ALL_ON_DEVICE 7u
+
+zhsm_status zhsm_create(int device, zhsm_handle **out);
+void zhsm_destroy(zhsm_handle *h);
+const char *zhsm_last_error(zhsm_handle *h);
+
+/* Sets the sensor geometry; builds the device-side tables (double cos/sin of the beam angles computed on the
+ * host with libm so Cartesian points are bit-identical to ld_compute_cartesian, and the GF(2) matrices that
+ * let ld_corr_hash be evaluated in parallel). */
+zhsm_status zhsm_set_laser(zhsm_handle *h, const zhsm_laser *laser);
+
+void zhsm_plicp_default_params(zhsm_plicp_params *p, int pm_min_range_cm, int pm_max_range_cm);
+
+/* CCanonicalMatcher::median_filter (ZHCanonical_Matcher.cpp:159-189) == CPolarMatch::pm_median_filter
+ * (ZHPolar_Match.cpp:1610-1639), in place over S scans. */
+zhsm_status zhsm_median_filter_batch(zhsm_handle *h, float *scans, int S, unsigned flags, void *cuda_stream);
+
+/* Batched CCanonicalMatcher::FMatch(LDP,LDP) (ZHCanonical_Matcher.cpp:251-285): fromPMScan2LDP on both scans
+ * (:193-227) + sm_icp (:274).  Scans must already be median filtered (the wrapper filters each scan once when
+ * it arrives, :233-237).  first_guess may be NULL (= 0,0,0 as :270-272) or [B][3] doubles (m,m,rad).
+ * corr_j1/corr_j2 may be NULL or [B][n] int16 (-1 = no correspondence). */
+zhsm_status zhsm_plicp_batch(zhsm_handle *h, const float *scans, int S, const int32_t *ref_idx,
+                             const int32_t *sens_idx, const double *first_guess, int B,
+                             const zhsm_plicp_params *params, zhsm_result *results, int16_t *corr_j1,
+                             int16_t *corr_j2, unsigned flags, void *cuda_stream);
+
+/* blocks until everything queued on the handle's stream (or the given one) is done */
+zhsm_status zhsm_sync(zhsm_handle *h, void *cuda_stream);
+
+/* number of kernels this handle has launched since creation (bench.py's gpu_launches) */
+uint64_t zhsm_launch_count(zhsm_handle *h);
+/* elapsed GPU milliseconds of the most recent batch call's main kernel, measured with CUDA events on
+ * the launching stream (valid after zhsm_sync) */
+float zhsm_last_kernel_ms(zhsm_handle *h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ZHSM_H */

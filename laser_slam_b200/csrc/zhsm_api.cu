@@ -1,0 +1,298 @@
+// laser_slam_b200/csrc/zhsm_api.cu -- the C-ABI layer of libzhsm.so (include/zhsm.h) + small kernels.
+// Host logic only: argument checks, staging of host buffers, table construction, launches.  No CPU fallback:
+// every compute entry fails with ZHSM_ERR_CUDA when no usable device exists.
+#include <math.h>
+#include <string.h>
+
+#include "zhsm_internal.h"
+
+// ---------------------------------------------------------------------------------------------------------
+// 5-tap in-place median filter: CCanonicalMatcher::median_filter (src/zhcsm/ZHCanonical_Matcher.cpp:159-189)
+// == CPolarMatch::pm_median_filter (src/zhpsm/ZHPolar_Match.cpp:1610-1639).  The write-back makes taps i-2,i-1
+// already-filtered values, i.e. a left-to-right recurrence: one thread walks one scan, the window lives in
+// registers.  A row is touched once (32-byte sectors are reused by the walking thread through L1).
+// ---------------------------------------------------------------------------------------------------------
+__global__ void median_filter_kernel(float *scans, int S, int n) {
+    int sidx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (sidx >= S) return;
+    float *r = scans + (size_t)sidx * n;
+    // window = {f[i-2], f[i-1], r[i], r[i+1], r[i+2]} with clamped indices; f = filtered
+    float r0 = r[0];
+    float m2 = r0, m1 = r0;                    // taps i-2, i-1 (clamped to index 0 -> the ORIGINAL r[0] until written)
+    float c0 = r0;
+    float p1 = n > 1 ? r[1] : r0;
+    float p2 = n > 2 ? r[2] : p1;
+    for (int i = 0; i < n; i++) {
+        float w0 = m2, w1 = m1, w2 = c0, w3 = p1, w4 = p2;
+        // bubble sort is a pure compare/swap sort: any exact median-of-5 gives the same value
+        float a = w0, b = w1, c = w2, d = w3, e = w4, t;
+#define ZH_SW(x, y) if (x > y) { t = x; x = y; y = t; }
+        ZH_SW(a, b) ZH_SW(c, d) ZH_SW(a, c) ZH_SW(b, d)   // a = min(a..d), d = max(a..d)
+        ZH_SW(b, c)                                       // a <= b <= c <= d
+        // insert e: median of {a,b,c,d,e} = median of {b, c, e} when a<=b<=c<=d
+        float med = e < b ? b : (e > c ? c : e);
+#undef ZH_SW
+        r[i] = med;
+        // slide: taps for i+1 are f[i-1], f[i], r[i+1], r[i+2], r[i+3]; clamping at 0 uses f[0] once written
+        if (i == 0) { m2 = med; m1 = med; }   // indices -1 and 0 both clamp to 0, which now holds f[0]
+        else { m2 = m1; m1 = med; }
+        c0 = p1;
+        p1 = p2;
+        int nx = i + 3;
+        p2 = r[nx < n ? nx : n - 1];
+        // clamped right taps read r[n-1], still unfiltered until i reaches n-1
+    }
+}
+
+cudaError_t median_filter_launch(float *scans, int S, int n, cudaStream_t st) {
+    int nt = 128;
+    median_filter_kernel<<<(S + nt - 1) / nt, nt, 0, st>>>(scans, S, n);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// handle
+// ---------------------------------------------------------------------------------------------------------
+static zhsm_status stage(zhsm_handle *h, int slot, size_t bytes, void **out) {
+    if (h->stage_bytes[slot] < bytes) {
+        if (h->d_stage[slot]) cudaFree(h->d_stage[slot]);
+        h->d_stage[slot] = nullptr;
+        h->stage_bytes[slot] = 0;
+        size_t cap = bytes + bytes / 4 + 256;
+        if (cudaMalloc(&h->d_stage[slot], cap) != cudaSuccess) {
+            cudaGetLastError();
+            h->err = "cudaMalloc(staging) failed";
+            return ZHSM_ERR_NOMEM;
+        }
+        h->stage_bytes[slot] = cap;
+    }
+    *out = h->d_stage[slot];
+    return ZHSM_OK;
+}
+
+extern "C" zhsm_status zhsm_create(int device, zhsm_handle **out) {
+    if (!out) return ZHSM_ERR_ARG;
+    *out = nullptr;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0 || device < 0 || device >= count) {
+        cudaGetLastError();
+        return ZHSM_ERR_CUDA;  // no CPU fallback by design
+    }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return ZHSM_ERR_CUDA;
+    if (prop.major < 10) return ZHSM_ERR_UNSUPPORTED;  // sm_100a cubins only
+    if (cudaSetDevice(device) != cudaSuccess) return ZHSM_ERR_CUDA;
+    zhsm_handle *h = new zhsm_handle();
+    h->device = device;
+    h->sm_count = prop.multiProcessorCount;
+    if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreate(&h->ev0) != cudaSuccess || cudaEventCreate(&h->ev1) != cudaSuccess) {
+        delete h;
+        return ZHSM_ERR_CUDA;
+    }
+    *out = h;
+    return ZHSM_OK;
+}
+
+extern "C" void zhsm_destroy(zhsm_handle *h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    for (int i = 0; i < 8; i++) if (h->d_stage[i]) cudaFree(h->d_stage[i]);
+    if (h->d_cs) cudaFree(h->d_cs);
+    if (h->d_hashmat) cudaFree(h->d_hashmat);
+    if (h->ev0) cudaEventDestroy(h->ev0);
+    if (h->ev1) cudaEventDestroy(h->ev1);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+extern "C" const char *zhsm_last_error(zhsm_handle *h) { return h ? h->err.c_str() : "null handle"; }
+
+extern "C" uint64_t zhsm_launch_count(zhsm_handle *h) { return h ? h->launches : 0; }
+
+extern "C" float zhsm_last_kernel_ms(zhsm_handle *h) {
+    if (!h || !h->ev_valid) return -1.f;
+    float ms = -1.f;
+    if (cudaEventElapsedTime(&ms, h->ev0, h->ev1) != cudaSuccess) { cudaGetLastError(); return -1.f; }
+    return ms;
+}
+
+extern "C" zhsm_status zhsm_sync(zhsm_handle *h, void *cuda_stream) {
+    if (!h) return ZHSM_ERR_ARG;
+    cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : h->stream;
+    ZHSM_CUDA_TRY(h, cudaStreamSynchronize(st));
+    return ZHSM_OK;
+}
+
+extern "C" zhsm_status zhsm_set_laser(zhsm_handle *h, const zhsm_laser *laser) {
+    if (!h || !laser) return ZHSM_ERR_ARG;
+    if (laser->n < 10 || laser->n > ZHSM_MAX_BEAMS) { h->err = "laser.n out of range [10,4096]"; return ZHSM_ERR_ARG; }
+    ZHSM_CUDA_TRY(h, cudaSetDevice(h->device));
+    const int n = laser->n;
+    std::vector<double2> cs(n);
+    for (int i = 0; i < n; i++) {
+        // theta[i] exactly as fromPMScan2LDP (:210): float arithmetic, then widened; cos/sin by the host libm
+        float thf = laser->fi_min + laser->dfi * (float)(unsigned)i;
+        double th = (double)thf;
+        cs[i].x = cos(th);
+        cs[i].y = sin(th);
+    }
+    if (h->d_cs) { cudaFree(h->d_cs); h->d_cs = nullptr; }
+    ZHSM_CUDA_TRY(h, cudaMalloc(&h->d_cs, sizeof(double2) * n));
+    ZHSM_CUDA_TRY(h, cudaMemcpy(h->d_cs, cs.data(), sizeof(double2) * n, cudaMemcpyHostToDevice));
+    h->laser = *laser;
+    h->have_laser = true;
+    return ZHSM_OK;
+}
+
+// CCanonicalMatcher::sm_init (src/zhcsm/ZHCanonical_Matcher.cpp:83-157)
+extern "C" void zhsm_plicp_default_params(zhsm_plicp_params *p, int pm_min_range_cm, int pm_max_range_cm) {
+    memset(p, 0, sizeof(*p));
+    p->min_reading = pm_min_range_cm / 100.;
+    p->max_reading = pm_max_range_cm / 100.;
+    p->max_angular_correction_deg = 45;
+    p->max_linear_correction = 0.5;
+    p->max_iterations = 10;
+    p->epsilon_xy = 0.001;
+    p->epsilon_theta = 0.001;
+    p->max_correspondence_dist = 2;
+    p->sigma = 0.04;
+    p->use_corr_tricks = 1;
+    p->restart = 1;
+    p->restart_threshold_mean_error = 0.01;
+    p->restart_dt = 0.01;
+    p->restart_dtheta = 0.0261799;
+    p->use_point_to_line_distance = 1;
+    p->outliers_maxPerc = 0.95;
+    p->outliers_adaptive_order = 0.7;
+    p->outliers_adaptive_mult = 2.0;
+    p->outliers_remove_doubles = 1;
+    p->do_compute_covariance = 0;
+}
+
+extern "C" zhsm_status zhsm_median_filter_batch(zhsm_handle *h, float *scans, int S, unsigned flags, void *cuda_stream) {
+    if (!h || !scans || S < 0) return ZHSM_ERR_ARG;
+    if (!h->have_laser) { h->err = "zhsm_set_laser not called"; return ZHSM_ERR_ARG; }
+    if (S == 0) return ZHSM_OK;
+    ZHSM_CUDA_TRY(h, cudaSetDevice(h->device));
+    cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : h->stream;
+    const int n = h->laser.n;
+    float *d = scans;
+    size_t bytes = sizeof(float) * (size_t)S * n;
+    if (!(flags & ZHSM_SCANS_ON_DEVICE)) {
+        void *p;
+        zhsm_status s = stage(h, 0, bytes, &p);
+        if (s != ZHSM_OK) return s;
+        d = (float *)p;
+        ZHSM_CUDA_TRY(h, cudaMemcpyAsync(d, scans, bytes, cudaMemcpyHostToDevice, st));
+    }
+    ZHSM_CUDA_TRY(h, median_filter_launch(d, S, n, st));
+    h->launches++;
+    if (!(flags & ZHSM_SCANS_ON_DEVICE)) {
+        ZHSM_CUDA_TRY(h, cudaMemcpyAsync(scans, d, bytes, cudaMemcpyDeviceToHost, st));
+        ZHSM_CUDA_TRY(h, cudaStreamSynchronize(st));
+    }
+    return ZHSM_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// batched PL-ICP
+// ---------------------------------------------------------------------------------------------------------
+extern "C" zhsm_status zhsm_plicp_batch(zhsm_handle *h, const float *scans, int S, const int32_t *ref_idx,
+                                        const int32_t *sens_idx, const double *first_guess, int B,
+                                        const zhsm_plicp_params *params, zhsm_result *results, int16_t *corr_j1,
+                                        int16_t *corr_j2, unsigned flags, void *cuda_stream) {
+    if (!h) return ZHSM_ERR_ARG;
+    if (!scans || !ref_idx || !sens_idx || !results || S <= 0 || B < 0 || ((corr_j1 == nullptr) != (corr_j2 == nullptr))) {
+        h->err = "zhsm_plicp_batch: bad argument";
+        return ZHSM_ERR_ARG;
+    }
+    if (!h->have_laser) { h->err = "zhsm_set_laser not called"; return ZHSM_ERR_ARG; }
+    if (B == 0) return ZHSM_OK;
+    zhsm_plicp_params P;
+    if (params) P = *params; else zhsm_plicp_default_params(&P, h->laser.min_range_cm, h->laser.max_range_cm);
+    if (P.use_corr_tricks != 1 || P.use_point_to_line_distance != 1) {
+        h->err = "only use_corr_tricks=1 / use_point_to_line_distance=1 (the reference's settings) are implemented";
+        return ZHSM_ERR_UNSUPPORTED;
+    }
+    if (P.do_compute_covariance) { h->err = "do_compute_covariance not implemented yet"; return ZHSM_ERR_UNSUPPORTED; }
+    if (P.max_iterations < 1 || P.max_iterations > ZHSM_MAX_ITER) { h->err = "max_iterations out of [1,64]"; return ZHSM_ERR_ARG; }
+    ZHSM_CUDA_TRY(h, cudaSetDevice(h->device));
+    cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : h->stream;
+    const int n = h->laser.n;
+
+    PlicpArgs a;
+    memset(&a, 0, sizeof(a));
+    a.B = B;
+    a.P = P;
+    a.L.n = n; a.L.fi_min = h->laser.fi_min; a.L.dfi = h->laser.dfi;
+    a.L.min_range_cm = h->laser.min_range_cm; a.L.max_range_cm = h->laser.max_range_cm;
+    a.L.min_valid_points = h->laser.min_valid_points; a.L.scan_window = h->laser.scan_window;
+    a.cs = h->d_cs;
+    a.hashmat = h->d_hashmat;
+
+    // ld_valid_fields' per-scan-geometry checks (laser_data.c): nrays, fov, theta[] consistent by construction
+    {
+        float thf0 = h->laser.fi_min, thf1 = h->laser.fi_min + h->laser.dfi * (float)(unsigned)(n - 1);
+        double fov = (double)thf1 - (double)thf0;
+        const double PI = 3.14159265358979323846;
+        if (n < 10 || n > 10000 || !(fov >= 20.0 * PI / 180.0 && fov <= 2.01 * PI)) {
+            h->err = "geometry rejected by ld_valid_fields (fov must be in [20deg, 2.01*pi], 10<=n<=10000)";
+            return ZHSM_ERR_ARG;
+        }
+    }
+    void *p;
+    zhsm_status s;
+    const size_t scan_bytes = sizeof(float) * (size_t)S * n;
+    if (flags & ZHSM_SCANS_ON_DEVICE) a.scans = scans;
+    else {
+        if ((s = stage(h, 0, scan_bytes, &p)) != ZHSM_OK) return s;
+        ZHSM_CUDA_TRY(h, cudaMemcpyAsync(p, scans, scan_bytes, cudaMemcpyHostToDevice, st));
+        a.scans = (const float *)p;
+    }
+    if (flags & ZHSM_JOBS_ON_DEVICE) { a.ref_idx = ref_idx; a.sens_idx = sens_idx; a.first_guess = first_guess; }
+    else {
+        for (int k = 0; k < B; k++)
+            if (ref_idx[k] < 0 || ref_idx[k] >= S || sens_idx[k] < 0 || sens_idx[k] >= S) {
+                h->err = "zhsm_plicp_batch: scan index out of range";
+                return ZHSM_ERR_ARG;
+            }
+        if ((s = stage(h, 1, sizeof(int32_t) * 2 * (size_t)B, &p)) != ZHSM_OK) return s;
+        int32_t *di = (int32_t *)p;
+        ZHSM_CUDA_TRY(h, cudaMemcpyAsync(di, ref_idx, sizeof(int32_t) * B, cudaMemcpyHostToDevice, st));
+        ZHSM_CUDA_TRY(h, cudaMemcpyAsync(di + B, sens_idx, sizeof(int32_t) * B, cudaMemcpyHostToDevice, st));
+        a.ref_idx = di; a.sens_idx = di + B;
+        if (first_guess) {
+            if ((s = stage(h, 2, sizeof(double) * 3 * (size_t)B, &p)) != ZHSM_OK) return s;
+            ZHSM_CUDA_TRY(h, cudaMemcpyAsync(p, first_guess, sizeof(double) * 3 * B, cudaMemcpyHostToDevice, st));
+            a.first_guess = (const double *)p;
+        }
+    }
+    const size_t corr_bytes = sizeof(int16_t) * (size_t)B * n;
+    if (flags & ZHSM_RESULTS_ON_DEVICE) { a.results = results; a.corr_j1 = corr_j1; a.corr_j2 = corr_j2; }
+    else {
+        if ((s = stage(h, 3, sizeof(zhsm_result) * (size_t)B, &p)) != ZHSM_OK) return s;
+        a.results = (zhsm_result *)p;
+        if (corr_j1) {
+            if ((s = stage(h, 4, 2 * corr_bytes, &p)) != ZHSM_OK) return s;
+            a.corr_j1 = (int16_t *)p;
+            a.corr_j2 = a.corr_j1 + (size_t)B * n;
+        }
+    }
+    ZHSM_CUDA_TRY(h, cudaEventRecord(h->ev0, st));
+    int launched = 0;
+    ZHSM_CUDA_TRY(h, plicp_launch(a, h->sm_count, st, &launched));
+    h->launches += launched;
+    ZHSM_CUDA_TRY(h, cudaEventRecord(h->ev1, st));
+    h->ev_valid = true;
+    if (!(flags & ZHSM_RESULTS_ON_DEVICE)) {
+        ZHSM_CUDA_TRY(h, cudaMemcpyAsync(results, a.results, sizeof(zhsm_result) * (size_t)B, cudaMemcpyDeviceToHost, st));
+        if (corr_j1) {
+            ZHSM_CUDA_TRY(h, cudaMemcpyAsync(corr_j1, a.corr_j1, corr_bytes, cudaMemcpyDeviceToHost, st));
+            ZHSM_CUDA_TRY(h, cudaMemcpyAsync(corr_j2, a.corr_j2, corr_bytes, cudaMemcpyDeviceToHost, st));
+        }
+        ZHSM_CUDA_TRY(h, cudaStreamSynchronize(st));  // host results are ready on return
+    }
+    return ZHSM_OK;
+}

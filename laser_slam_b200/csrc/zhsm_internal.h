@@ -1,0 +1,66 @@
+// laser_slam_b200/csrc/zhsm_internal.h -- internals shared by the kernels and the C-ABI layer.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/zhsm.h"
+
+#define ZHSM_MAX_BEAMS 4096
+#define ZHSM_MAX_ITER 64
+
+struct zhsm_handle {
+    int device = 0;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    uint64_t launches = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool ev_valid = false;
+
+    bool have_laser = false;
+    zhsm_laser laser{};
+    double2 *d_cs = nullptr;      // [n] (cos theta_i, sin theta_i), host libm, double
+    uint32_t *d_hashmat = nullptr; // GF(2) matrices for the parallel ld_corr_hash, see plicp_sm100.cu
+    int hash_chunk = 0, hash_chunks = 0;
+
+    // staging for host-pointer calls
+    void *d_stage[8] = {nullptr};
+    size_t stage_bytes[8] = {0};
+};
+
+// device-side geometry passed by value to kernels
+struct LaserDev {
+    int n;
+    float fi_min, dfi;
+    int min_range_cm, max_range_cm;
+    int min_valid_points, scan_window;
+};
+
+struct PlicpArgs {
+    const float *scans;      // [S][n]
+    const int32_t *ref_idx;  // [B]
+    const int32_t *sens_idx; // [B]
+    const double *first_guess; // [B][3] or null
+    zhsm_result *results;    // [B]
+    int16_t *corr_j1, *corr_j2; // [B][n] or null
+    const double2 *cs;       // [n]
+    const uint32_t *hashmat;
+    int B;
+    LaserDev L;
+    zhsm_plicp_params P;
+};
+
+cudaError_t plicp_launch(const PlicpArgs &a, int sm_count, cudaStream_t st, int *launched);
+cudaError_t median_filter_launch(float *scans, int S, int n, cudaStream_t st);
+
+#define ZHSM_CUDA_TRY(h, expr)                                                              \
+    do {                                                                                    \
+        cudaError_t _e = (expr);                                                            \
+        if (_e != cudaSuccess) {                                                            \
+            (h)->err = std::string(#expr) + ": " + cudaGetErrorString(_e);                  \
+            return ZHSM_ERR_CUDA;                                                           \
+        }                                                                                   \
+    } while (0)

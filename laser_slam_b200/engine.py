@@ -1,0 +1,200 @@
+"""ctypes binding of include/zhsm.h.  Host buffers are numpy arrays; device buffers are anything with
+`data_ptr()` (torch CUDA tensors) -- only raw pointers cross the boundary."""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+PM_PI = 3.141592654  # src/zhpsm/PolarParameter.h:38 (the reference's truncated pi)
+PM_D2R = PM_PI / 180.0
+
+# Base_PARAM tables (src/zhpsm/PolarParameter.h:70-83): points, fov_deg, max_range_cm, min_valid, window, fi_min_deg
+LASER_TABLE = {
+    "LMS511": (361, 180, 5000, 80, 40, 0),
+    "LMS211": (181, 180, 5000, 40, 20, -90),
+    "LMS151": (541, 270, 5000, 100, 50, -45),
+}
+
+
+class ZhsmError(RuntimeError):
+    pass
+
+
+class Laser(C.Structure):
+    _fields_ = [("n", C.c_int32), ("fi_min", C.c_float), ("dfi", C.c_float), ("min_range_cm", C.c_int32),
+                ("max_range_cm", C.c_int32), ("min_valid_points", C.c_int32), ("scan_window", C.c_int32),
+                ("reserved", C.c_int32)]
+
+
+def laser_from_table(name, fi_min=None, max_range_cm=None):
+    """Base_PARAM ctor arithmetic (PolarParameter.h:57-66): pm_dfi = (fov*D2R)/(points-1.0) narrowed to float."""
+    pts, fov, mx, mv, win, fmin_deg = LASER_TABLE[name]
+    lz = Laser()
+    lz.n = pts
+    lz.fi_min = np.float32(fmin_deg * PM_D2R) if fi_min is None else np.float32(fi_min)
+    lz.dfi = np.float32((fov * PM_D2R) / (pts - 1.0))
+    lz.min_range_cm = 10
+    lz.max_range_cm = mx if max_range_cm is None else int(max_range_cm)
+    lz.min_valid_points = mv
+    lz.scan_window = win
+    return lz
+
+
+class PlicpParams(C.Structure):
+    _fields_ = [(k, C.c_double) for k in (
+        "max_angular_correction_deg", "max_linear_correction", "epsilon_xy", "epsilon_theta",
+        "max_correspondence_dist", "sigma", "restart_threshold_mean_error", "restart_dt", "restart_dtheta",
+        "outliers_maxPerc", "outliers_adaptive_order", "outliers_adaptive_mult", "min_reading", "max_reading")] + [
+        (k, C.c_int32) for k in ("max_iterations", "use_corr_tricks", "restart", "use_point_to_line_distance",
+                                 "outliers_remove_doubles", "do_compute_covariance")] + [("reserved", C.c_int32 * 2)]
+
+
+RESULT_DTYPE = np.dtype([("x", "f8", 3), ("cov", "f8", 6), ("error", "f8"), ("valid", "i4"), ("iterations", "i4"),
+                         ("nvalid", "i4"), ("status", "i4"), ("goodness", "f4"), ("quality", "f4"),
+                         ("corr_hash", "u4"), ("n_loops", "i4"), ("reserved", "i4", 4)])
+assert RESULT_DTYPE.itemsize == 128
+
+SCANS_ON_DEVICE, JOBS_ON_DEVICE, RESULTS_ON_DEVICE, ALL_ON_DEVICE = 1, 2, 4, 7
+
+_lib = None
+
+
+def lib_path():
+    return os.path.join(_HERE, "libzhsm.so")
+
+
+def load_library():
+    """Loads libzhsm.so; raises loudly when it is missing (there is no fallback path)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    p = lib_path()
+    if not os.path.exists(p):
+        raise ZhsmError("libzhsm.so is not built: run `python -m laser_slam_b200.build` (nvcc, sm_100a)")
+    L = C.CDLL(p)
+    vp, i32, u32 = C.c_void_p, C.c_int, C.c_uint
+    L.zhsm_create.argtypes = [i32, C.POINTER(vp)]
+    L.zhsm_destroy.argtypes = [vp]
+    L.zhsm_destroy.restype = None
+    L.zhsm_last_error.argtypes = [vp]
+    L.zhsm_last_error.restype = C.c_char_p
+    L.zhsm_set_laser.argtypes = [vp, C.POINTER(Laser)]
+    L.zhsm_plicp_default_params.argtypes = [C.POINTER(PlicpParams), i32, i32]
+    L.zhsm_plicp_default_params.restype = None
+    L.zhsm_median_filter_batch.argtypes = [vp, vp, i32, u32, vp]
+    L.zhsm_plicp_batch.argtypes = [vp, vp, i32, vp, vp, vp, i32, C.POINTER(PlicpParams), vp, vp, vp, u32, vp]
+    L.zhsm_sync.argtypes = [vp, vp]
+    L.zhsm_launch_count.argtypes = [vp]
+    L.zhsm_launch_count.restype = C.c_uint64
+    L.zhsm_last_kernel_ms.argtypes = [vp]
+    L.zhsm_last_kernel_ms.restype = C.c_float
+    _lib = L
+    return L
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if hasattr(a, "data_ptr"):
+        return a.data_ptr()
+    return a.ctypes.data
+
+
+def _is_dev(a):
+    return hasattr(a, "data_ptr")
+
+
+class Engine:
+    """One handle = one GPU + one stream.  Mirrors the three matcher classes' batched form."""
+
+    def __init__(self, device=0):
+        self.L = load_library()
+        h = C.c_void_p()
+        st = self.L.zhsm_create(int(device), C.byref(h))
+        if st != 0:
+            raise ZhsmError(f"zhsm_create(device={device}) failed with status {st}: no usable sm_100 GPU "
+                            "(this engine has no CPU fallback)")
+        self.h = h
+        self.laser = None
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.zhsm_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, st, what):
+        if st != 0:
+            raise ZhsmError(f"{what}: status {st}: {self.L.zhsm_last_error(self.h).decode()}")
+
+    def set_laser(self, laser):
+        self.laser = laser
+        self._check(self.L.zhsm_set_laser(self.h, C.byref(laser)), "zhsm_set_laser")
+
+    def default_plicp_params(self):
+        p = PlicpParams()
+        self.L.zhsm_plicp_default_params(C.byref(p), self.laser.min_range_cm, self.laser.max_range_cm)
+        return p
+
+    def median_filter(self, scans, stream=None):
+        """In place.  numpy float32 [S][n] (host) or a CUDA tensor."""
+        dev = _is_dev(scans)
+        if not dev:
+            assert scans.dtype == np.float32 and scans.flags.c_contiguous
+        S = scans.shape[0]
+        self._check(self.L.zhsm_median_filter_batch(self.h, _ptr(scans), S, SCANS_ON_DEVICE if dev else 0, stream),
+                    "zhsm_median_filter_batch")
+        return scans
+
+    def plicp(self, scans, ref_idx, sens_idx, first_guess=None, params=None, results=None, want_corr=False,
+              stream=None):
+        """Batched CCanonicalMatcher::FMatch on median-filtered scans.  Host (numpy) or device (torch) buffers;
+        all job arrays must live on the same side."""
+        n = self.laser.n
+        dev_scans = _is_dev(scans)
+        dev_jobs = _is_dev(ref_idx)
+        B = int(ref_idx.shape[0])
+        S = int(scans.shape[0])
+        flags = (SCANS_ON_DEVICE if dev_scans else 0) | (JOBS_ON_DEVICE if dev_jobs else 0)
+        if not dev_scans:
+            assert scans.dtype == np.float32 and scans.flags.c_contiguous and scans.shape[1] == n
+        if not dev_jobs:
+            ref_idx = np.ascontiguousarray(ref_idx, np.int32)
+            sens_idx = np.ascontiguousarray(sens_idx, np.int32)
+            if first_guess is not None:
+                first_guess = np.ascontiguousarray(first_guess, np.float64)
+        j1 = j2 = None
+        if results is None:
+            results = np.zeros(B, RESULT_DTYPE)
+        if _is_dev(results):
+            flags |= RESULTS_ON_DEVICE
+            if want_corr:
+                import torch
+                j1 = torch.empty((B, n), dtype=torch.int16, device=results.device)
+                j2 = torch.empty((B, n), dtype=torch.int16, device=results.device)
+        elif want_corr:
+            j1 = np.zeros((B, n), np.int16)
+            j2 = np.zeros((B, n), np.int16)
+        st = self.L.zhsm_plicp_batch(self.h, _ptr(scans), S, _ptr(ref_idx), _ptr(sens_idx), _ptr(first_guess), B,
+                                     C.byref(params) if params is not None else None, _ptr(results), _ptr(j1),
+                                     _ptr(j2), flags, stream)
+        self._check(st, "zhsm_plicp_batch")
+        if want_corr:
+            return results, j1, j2
+        return results
+
+    def sync(self, stream=None):
+        self._check(self.L.zhsm_sync(self.h, stream), "zhsm_sync")
+
+    def launch_count(self):
+        return int(self.L.zhsm_launch_count(self.h))
+
+    def last_kernel_ms(self):
+        return float(self.L.zhsm_last_kernel_ms(self.h))
