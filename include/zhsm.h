@@ -100,6 +100,11 @@ typedef struct zhsm_result {
 #define ZHSM_JOBS_ON_DEVICE 2u    /* ref_idx/sens_idx/first_guess pointers are device memory */
 #define ZHSM_RESULTS_ON_DEVICE 4u /* results (and corr outputs) are device memory */
 #define ZHSM_ALL_ON_DEVICE 7u
+/* zhsm_plicp_batch only: median-filter the whole scan pool first (the device copy when the pool is a host
+ * buffer), i.e. the CCanonicalMatcher::FMatch(PMScan*,PMScan*,bFirst=true) flow (:229-249) in one call.
+ * With ZHSM_WRITEBACK_SCANS a host pool receives the filtered ranges back, like FMatch mutates lsa->r. */
+#define ZHSM_FILTER_SCANS 8u
+#define ZHSM_WRITEBACK_SCANS 16u
 
 zhsm_status zhsm_create(int device, zhsm_handle **out);
 void zhsm_destroy(zhsm_handle *h);
@@ -133,6 +138,15 @@ uint64_t zhsm_launch_count(zhsm_handle *h);
 /* elapsed GPU milliseconds of the most recent batch call's main kernel, measured with CUDA events on
  * the launching stream (valid after zhsm_sync) */
 float zhsm_last_kernel_ms(zhsm_handle *h);
+
+/* ---- workload tooling (bench.py / tests; not part of the reference's interface) ----------------------------
+ * Synthetic scan pairs of SURVEY 8d (C4/C5) generated on the device: scans[2p] = ref, scans[2p+1] = sens taken
+ * from a pose displaced by truth[p] = (dx,dy,dtheta) uniform in +-dmax.  Philox counter = first_pair + p. */
+zhsm_status zhsm_synth_pairs(zhsm_handle *h, float *d_scans, double *d_truth, long long first_pair, int npairs,
+                             float dmax_xy_m, float dmax_th_rad, float noise_m, float dropout,
+                             unsigned long long seed, void *cuda_stream);
+/* measured CUDA-core FMA peak in TFLOP/s: which = 32 (FFMA) or 64 (DFMA) */
+double zhsm_fp_peak_tflops(zhsm_handle *h, int which);
 
 #ifdef __cplusplus
 }

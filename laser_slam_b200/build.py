@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libzhsm.so")
-SOURCES = ["zhsm_api.cu", "plicp_sm100.cu"]
+SOURCES = ["zhsm_api.cu", "plicp_sm100.cu", "synth_sm100.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 # -fmad=false: the reference links an x86-64 (no FMA contraction) CSM; every a*b+c must round twice like it does
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-fmad=false",
@@ -18,20 +18,42 @@ def newest(paths):
 
 
 def build(force=False, verbose=False):
-    srcs = [os.path.join(CSRC, s) for s in SOURCES]
-    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(HERE, "..", "include", "zhsm.h")]
-    if not force and os.path.exists(OUT) and os.path.getmtime(OUT) >= newest(deps):
-        return OUT
+    """Per-source objects (csrc/_obj/*.o, rebuilt only when a dependency is newer) linked into libzhsm.so."""
+    objdir = os.path.join(CSRC, "_obj")
+    os.makedirs(objdir, exist_ok=True)
+    headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))]
+    headers.append(os.path.join(HERE, "..", "include", "zhsm.h"))
     ccbin = [] if not os.path.exists("/usr/bin/g++") else ["-ccbin", "/usr/bin/g++"]
-    cmd = [NVCC] + ccbin + FLAGS + ["-o", OUT] + srcs
-    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     log = os.path.join(HERE, "build.log")
-    with open(log, "w") as f:
-        f.write(" ".join(cmd) + "\n" + r.stdout)
-    if verbose or r.returncode != 0:
-        print(r.stdout)
-    if r.returncode != 0:
-        raise RuntimeError("nvcc failed, see " + log)
+    objs, rebuilt = [], False
+    procs = []
+    for s in SOURCES:
+        src = os.path.join(CSRC, s)
+        obj = os.path.join(objdir, s.replace(".cu", ".o"))
+        objs.append(obj)
+        if force or not os.path.exists(obj) or os.path.getmtime(obj) < newest([src] + headers):
+            cmd = [NVCC] + ccbin + [f for f in FLAGS if f != "-shared"] + ["-c", "-o", obj, src]
+            procs.append((s, cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
+            rebuilt = True
+    out_all = ""
+    for s, cmd, pr in procs:
+        out, _ = pr.communicate()
+        out_all += " ".join(cmd) + "\n" + out
+        if pr.returncode != 0:
+            print(out)
+            raise RuntimeError("nvcc failed on " + s)
+    if rebuilt or not os.path.exists(OUT):
+        cmd = [NVCC] + ccbin + ["-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", OUT] + objs
+        r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        out_all += " ".join(cmd) + "\n" + r.stdout
+        if r.returncode != 0:
+            print(r.stdout)
+            raise RuntimeError("link failed")
+    if out_all:
+        with open(log, "w") as f:
+            f.write(out_all)
+        if verbose:
+            print(out_all)
     return OUT
 
 

@@ -280,6 +280,12 @@ extern "C" zhsm_status zhsm_plicp_batch(zhsm_handle *h, const float *scans, int 
             a.corr_j2 = a.corr_j1 + (size_t)B * n;
         }
     }
+    if (flags & ZHSM_FILTER_SCANS) {
+        ZHSM_CUDA_TRY(h, median_filter_launch(const_cast<float *>(a.scans), S, n, st));
+        h->launches++;
+        if ((flags & ZHSM_WRITEBACK_SCANS) && !(flags & ZHSM_SCANS_ON_DEVICE))
+            ZHSM_CUDA_TRY(h, cudaMemcpyAsync(const_cast<float *>(scans), a.scans, scan_bytes, cudaMemcpyDeviceToHost, st));
+    }
     ZHSM_CUDA_TRY(h, cudaEventRecord(h->ev0, st));
     int launched = 0;
     ZHSM_CUDA_TRY(h, plicp_launch(a, h->sm_count, st, &launched));

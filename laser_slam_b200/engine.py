@@ -57,6 +57,7 @@ RESULT_DTYPE = np.dtype([("x", "f8", 3), ("cov", "f8", 6), ("error", "f8"), ("va
 assert RESULT_DTYPE.itemsize == 128
 
 SCANS_ON_DEVICE, JOBS_ON_DEVICE, RESULTS_ON_DEVICE, ALL_ON_DEVICE = 1, 2, 4, 7
+FILTER_SCANS, WRITEBACK_SCANS = 8, 16
 
 _lib = None
 
@@ -90,6 +91,10 @@ def load_library():
     L.zhsm_launch_count.restype = C.c_uint64
     L.zhsm_last_kernel_ms.argtypes = [vp]
     L.zhsm_last_kernel_ms.restype = C.c_float
+    L.zhsm_synth_pairs.argtypes = [vp, vp, vp, C.c_longlong, i32, C.c_float, C.c_float, C.c_float, C.c_float,
+                                   C.c_ulonglong, vp]
+    L.zhsm_fp_peak_tflops.argtypes = [vp, i32]
+    L.zhsm_fp_peak_tflops.restype = C.c_double
     _lib = L
     return L
 
@@ -154,7 +159,7 @@ class Engine:
         return scans
 
     def plicp(self, scans, ref_idx, sens_idx, first_guess=None, params=None, results=None, want_corr=False,
-              stream=None):
+              stream=None, filter_scans=False, writeback=False):
         """Batched CCanonicalMatcher::FMatch on median-filtered scans.  Host (numpy) or device (torch) buffers;
         all job arrays must live on the same side."""
         n = self.laser.n
@@ -163,6 +168,7 @@ class Engine:
         B = int(ref_idx.shape[0])
         S = int(scans.shape[0])
         flags = (SCANS_ON_DEVICE if dev_scans else 0) | (JOBS_ON_DEVICE if dev_jobs else 0)
+        flags |= (FILTER_SCANS if filter_scans else 0) | (WRITEBACK_SCANS if writeback else 0)
         if not dev_scans:
             assert scans.dtype == np.float32 and scans.flags.c_contiguous and scans.shape[1] == n
         if not dev_jobs:
@@ -189,6 +195,16 @@ class Engine:
         if want_corr:
             return results, j1, j2
         return results
+
+    def synth_pairs(self, d_scans, d_truth, first_pair, npairs, dmax_xy_m=0.10, dmax_th_rad=0.0872664626,
+                    noise_m=0.01, dropout=0.01, seed=20261104, stream=None):
+        """SURVEY 8d C4 generator, on the device: d_scans [2*npairs][n] float32, d_truth [npairs][3] float64."""
+        self._check(self.L.zhsm_synth_pairs(self.h, _ptr(d_scans), _ptr(d_truth), int(first_pair), int(npairs),
+                                            dmax_xy_m, dmax_th_rad, noise_m, dropout, int(seed), stream),
+                    "zhsm_synth_pairs")
+
+    def fp_peak_tflops(self, which):
+        return float(self.L.zhsm_fp_peak_tflops(self.h, int(which)))
 
     def sync(self, stream=None):
         self._check(self.L.zhsm_sync(self.h, stream), "zhsm_sync")

@@ -961,3 +961,24 @@ void orc_zhcsm_fmatch_batch(const float *scans, int n, const int *ref_idx, const
     for (int t = 0; t < nthreads; t++) pthread_create(&th[t], NULL, batch_worker, &jobs[t]);
     for (int t = 0; t < nthreads; t++) pthread_join(th[t], NULL);
 }
+
+/* median filter over S scans in place (wrapper :233-237 filters every scan once), nthreads pthreads */
+typedef struct { float *scans; int n, lo, hi; } mf_job;
+static void *mf_worker(void *arg) {
+    mf_job *j = (mf_job *)arg;
+    for (int k = j->lo; k < j->hi; k++) orc_median_filter(j->scans + (size_t)k * j->n, j->n);
+    return NULL;
+}
+void orc_median_filter_batch(float *scans, int S, int n, int nthreads) {
+    if (nthreads < 1) nthreads = 1;
+    if (nthreads > 256) nthreads = 256;
+    pthread_t th[256];
+    mf_job jobs[256];
+    for (int t = 0; t < nthreads; t++) {
+        mf_job jb = {scans, n, (int)((long long)S * t / nthreads), (int)((long long)S * (t + 1) / nthreads)};
+        jobs[t] = jb;
+    }
+    if (nthreads == 1) { mf_worker(&jobs[0]); return; }
+    for (int t = 0; t < nthreads; t++) pthread_create(&th[t], NULL, mf_worker, &jobs[t]);
+    for (int t = 0; t < nthreads; t++) pthread_join(th[t], NULL);
+}

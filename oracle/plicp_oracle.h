@@ -122,6 +122,8 @@ void orc_zhcsm_fmatch_batch(const float *scans, int n, const int *ref_idx, const
                             const double *first_guess_or_null /* [npairs][3] */,
                             orc_sm_result *out, int nthreads);
 
+void orc_median_filter_batch(float *scans, int S, int n, int nthreads);
+
 /* analysis helpers */
 unsigned int orc_ld_corr_hash(const orc_laser_data *ld);
 int orc_poly_greatest_real_root(const double a[5], double *root);

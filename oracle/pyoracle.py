@@ -90,6 +90,14 @@ def median_filter(r):
     return out
 
 
+def median_filter_batch(scans, nthreads=1):
+    """In place over a float32 [S][n] array."""
+    assert scans.dtype == np.float32 and scans.flags.c_contiguous
+    lib().orc_median_filter_batch.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
+    lib().orc_median_filter_batch(scans.ctypes.data, scans.shape[0], scans.shape[1], int(nthreads))
+    return scans
+
+
 def zhcsm_fmatch(ref_r_cm, sens_r_cm, fi_min, dfi, min_range_cm, max_range_cm, params=None, first_guess=None,
                  want_corr=False):
     """CCanonicalMatcher::FMatch on already median-filtered float32 cm ranges."""
