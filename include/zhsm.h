@@ -148,6 +148,10 @@ zhsm_status zhsm_synth_pairs(zhsm_handle *h, float *d_scans, double *d_truth, lo
 /* measured CUDA-core FMA peak in TFLOP/s: which = 32 (FFMA) or 64 (DFMA) */
 double zhsm_fp_peak_tflops(zhsm_handle *h, int which);
 
+/* test hook, host only: ld_corr_hash of a correspondence stream (j1 + 1000*j2, or -1) evaluated sequentially
+ * (seq) and with the kernel's chunk/GF(2)-matrix decomposition (par).  Returns 0 on success. */
+int zhsm_debug_corr_hash(const int32_t *stream, int n, uint32_t *seq, uint32_t *par);
+
 #ifdef __cplusplus
 }
 #endif

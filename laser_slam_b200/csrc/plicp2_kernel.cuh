@@ -1,0 +1,399 @@
+// laser_slam_b200/csrc/plicp2_kernel.cuh -- the PL-ICP kernel: load, icp_loop x (1+6 restarts), result record.
+// Replaces, per job, CCanonicalMatcher::FMatch(LDP,LDP) -> sm_icp (src/zhcsm/ZHCanonical_Matcher.cpp:251-285) with
+// the parameters of sm_init (:83-157).  SURVEY 8a-2..8a-8.  FP64 throughout (CSM is double end to end), -fmad=false.
+#pragma once
+#include "plicp2_common.cuh"
+#include "plicp2_search.cuh"
+#include "plicp2_select.cuh"
+#include "plicp2_solve.cuh"
+
+namespace plicp2 {
+
+// Per-thread state of its C rays i = k*T + t.
+template <int C>
+struct Rays {
+    int cj[C];      // j1 | j2 << 16 of the current correspondence (valid bit set) else -1
+    int spec[C];    // last_best this ray was (or will be) searched with
+    double key[C];  // dist2_j1 after the search, then the trim distance
+    unsigned valid; // bit k: ray k has a correspondence
+    unsigned sens;  // bit k: sens ray k exists and is valid
+};
+
+template <int T, int C>
+__device__ __forceinline__ void search_ray(const Smem &s, const LaserDev &L, int n, int k, int i, double x0,
+                                           double x1, double cs, double sn, double min_theta, double C1,
+                                           double maxd2, Rays<C> &R) {
+    const Ray ray = make_ray(s.sensp[i], x0, x1, cs, sn, min_theta, C1);
+    double d2 = 0;
+    int j2 = 0;
+    const int j1 = tricks_one(s, L, n, ray, R.spec[k], maxd2, &d2, &j2);
+    if (j1 >= 0) {
+        R.cj[k] = j1 | (j2 << 16);
+        R.key[k] = d2;
+        R.valid |= 1u << k;
+    } else {
+        R.cj[k] = -1;
+        R.valid &= ~(1u << k);
+    }
+    s.cj1[i] = (short)j1;
+}
+
+// find_correspondences_tricks for the whole scan: speculate / verify / re-search until the sequential result.
+template <int T, int C>
+__device__ __forceinline__ void find_correspondences(const Smem &s, const LaserDev &L, int n, double x0, double x1,
+                                                     double cs, double sn, double min_theta, double C1,
+                                                     double maxd2, Rays<C> &R) {
+    const int t = threadIdx.x;
+#pragma unroll
+    for (int k = 0; k < C; k++)
+        if (R.sens >> k & 1u) search_ray<T, C>(s, L, n, k, k * T + t, x0, x1, cs, sn, min_theta, C1, maxd2, R);
+    __syncthreads();
+    while (true) {
+        unsigned need = 0;
+#pragma unroll
+        for (int k = 0; k < C; k++) {
+            if (!(R.sens >> k & 1u)) continue;
+            int actual = -1;
+            for (int u = k * T + t - 1; u >= 0; u--) {
+                const int v = s.cj1[u];
+                if (v >= 0) { actual = v; break; }
+            }
+            if (actual != R.spec[k]) { need |= 1u << k; R.spec[k] = actual; }
+        }
+        if (!__syncthreads_or((int)need)) break;
+#pragma unroll
+        for (int k = 0; k < C; k++)
+            if (need >> k & 1u) search_ray<T, C>(s, L, n, k, k * T + t, x0, x1, cs, sn, min_theta, C1, maxd2, R);
+        __syncthreads();
+    }
+}
+
+template <int T, int C>
+__global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 2 : 1))) plicp2_kernel(PlicpArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    constexpr int NW = T / 32;
+    const int n = a.L.n;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int job = blockIdx.x;
+    const Smem s = carve(smem_raw, n, T);
+    Ctl *ctl = s.ctl;
+    const LaserDev L = a.L;
+    const zhsm_plicp_params &P = a.P;
+
+    // ---------------- load + fromPMScan2LDP + ld_valid_fields + ld_invalid_if_outside + ld_compute_cartesian
+    const float *ref_row = a.scans + (size_t)a.ref_idx[job] * n;
+    const float *sens_row = a.scans + (size_t)a.sens_idx[job] * n;
+    int bad_field = 0, nvf_ref = 0, nvf_sens = 0;
+    Rays<C> R;
+    R.valid = 0;
+    R.sens = 0;
+#pragma unroll
+    for (int k = 0; k < C; k++) {
+        R.cj[k] = -1;
+        R.spec[k] = -1;
+        R.key[k] = 0;
+        const int i = k * T + t;
+        if (i >= n) continue;
+        const double2 cs = a.cs[i];
+        double rr = reading_of(__ldg(ref_row + i), L, P, &bad_field);
+        nvf_ref += (rr != -1.0);
+        s.rr2[i] = rr >= 0 ? rr * rr : -1.0;
+        s.refp[i] = rr >= 0 ? make_double2(cs.x * rr, cs.y * rr) : make_double2(nan(""), nan(""));
+        double rs = reading_of(__ldg(sens_row + i), L, P, &bad_field);
+        nvf_sens += (rs != -1.0);
+        s.sensp[i] = rs >= 0 ? make_double2(cs.x * rs, cs.y * rs) : make_double2(nan(""), nan(""));
+        if (rs >= 0) R.sens |= 1u << k;
+        s.cj1[i] = -1;
+        s.cj2[i] = -1;
+    }
+    if (t == 0) {
+        for (int k = 0; k < 3; k++) ctl->x[0][k] = a.first_guess ? a.first_guess[3 * (size_t)job + k] : 0.0;
+        ctl->cs[0] = cos(ctl->x[0][2]);
+        ctl->sn[0] = sin(ctl->x[0][2]);
+    }
+    const int tot = block_sum<T>((nvf_ref << 16) | nvf_sens, ctl->ired, 0);
+    const int tot_bad = __syncthreads_or(bad_field);
+    const int tot_ref = tot >> 16, tot_sens = tot & 0xffff;
+    zhsm_result *res = a.results + job;
+    int16_t *oj1 = a.corr_j1 ? a.corr_j1 + (size_t)job * n : nullptr;
+    int16_t *oj2 = a.corr_j2 ? a.corr_j2 + (size_t)job * n : nullptr;
+    const bool guess_nan = isnan(ctl->x[0][0]) || isnan(ctl->x[0][1]) || isnan(ctl->x[0][2]);
+    const bool fields_bad = tot_bad || tot_ref < n * 0.10 || tot_sens < n * 0.10;
+    if (fields_bad || guess_nan) {
+        // ld_valid_fields failed (sm_icp returns valid=0 before iterating) or icp_loop refused a NaN first guess
+        if (t == 0) {
+            zhsm_result r = {};
+            r.status = ZHSM_JOB_INVALID_SCAN;
+            r.n_loops = fields_bad ? 0 : 1;
+            *res = r;
+        }
+        if (oj1) for (int i = t; i < n; i += T) { oj1[i] = -1; oj2[i] = -1; }
+        return;
+    }
+    build_jump_tables(s, n, t, T);
+    __syncthreads();
+
+    const double min_theta = (double)theta_f(L, 0), max_theta = (double)theta_f(L, n - 1);
+    const double C1 = (double)n / (max_theta - min_theta);
+    const double maxd2 = P.max_correspondence_dist * P.max_correspondence_dist;
+    const int max_it = P.max_iterations < ZHSM_MAX_ITER ? P.max_iterations : ZHSM_MAX_ITER;
+    const double fail_perc = 0.05;
+    const unsigned long long BIG = (unsigned long long)__double_as_longlong(1000000.0);
+
+    // sm_icp bookkeeping (icp.c), meaningful on thread 0
+    double best_x[3] = {0, 0, 0}, x_first[3] = {0, 0, 0}, best_error = 0;
+    int iterations = 0, nvalid0 = 0, n_loops = 0, restarted = 0, valid = 0, status = ZHSM_JOB_OK;
+
+    for (int loop = 0; loop < 7; loop++) {
+        int iteration = 0, all_ok = 1, par = 0, newest = 0;
+        for (iteration = 0; iteration < max_it; iteration++) {
+            const double x0 = ctl->x[par][0], x1 = ctl->x[par][1], x2 = ctl->x[par][2];
+            const double cs = ctl->cs[par], sn = ctl->sn[par];
+            for (int j = t; j < n; j += T) s.d2j[j] = BIG;
+            if (t == 0) ctl->hash_acc[iteration & 1] = 0;
+            find_correspondences<T, C>(s, L, n, x0, x1, cs, sn, min_theta, C1, maxd2, R);
+            // kill_outliers_double (icp_outliers.c): min dist2 per ref index
+            if (P.outliers_remove_doubles) {
+#pragma unroll
+                for (int k = 0; k < C; k++)
+                    if (R.valid >> k & 1u)
+                        atomicMin(&s.d2j[R.cj[k] & 0xffff], (unsigned long long)__double_as_longlong(R.key[k]));
+            }
+            const int num_corr = block_sum<T>(__popc(R.valid), ctl->ired, 1);
+            if (num_corr < fail_perc * n) { all_ok = 0; status = ZHSM_JOB_TOO_FEW_POINTS; break; }
+            if (P.outliers_remove_doubles) {
+#pragma unroll
+                for (int k = 0; k < C; k++)
+                    if (R.valid >> k & 1u) {
+                        const double dj = __longlong_as_double((long long)s.d2j[R.cj[k] & 0xffff]);
+                        if (R.key[k] > (3.0 * 3.0) * dj) R.valid &= ~(1u << k);
+                    }
+            }
+            for (int b = t; b < 256; b += T) s.hist[b] = 0;
+            const int kcnt = block_sum<T>(__popc(R.valid), ctl->ired, 2);  // all reads of d2j are done
+            // kill_outliers_trim: distance to the segment (j1,j2); keys go to shared memory
+#pragma unroll
+            for (int k = 0; k < C; k++) {
+                if (!(R.valid >> k & 1u)) continue;
+                const int i = k * T + t;
+                const double2 p = s.sensp[i];
+                const double wx = cs * p.x - sn * p.y + x0;
+                const double wy = sn * p.x + cs * p.y + x1;
+                const double2 q1 = s.refp[R.cj[k] & 0xffff], q2 = s.refp[R.cj[k] >> 16];
+                const double d = dist_to_segment(q1.x, q1.y, q2.x, q2.y, wx, wy);
+                R.key[k] = d;
+                s.d2j[i] = (unsigned long long)__double_as_longlong(d);
+            }
+            int order = (int)floor(kcnt * P.outliers_maxPerc);
+            order = order < kcnt - 1 ? order : kcnt - 1;
+            order = order > 0 ? order : 0;
+            int order2 = (int)floor(kcnt * P.outliers_adaptive_order);
+            order2 = order2 < kcnt - 1 ? order2 : kcnt - 1;
+            order2 = order2 > 0 ? order2 : 0;
+            double lim1, d_o2;
+            select2<T, C>(s, n, R.valid, order, order2, lim1, d_o2);
+            const double lim2 = P.outliers_adaptive_mult * d_o2;
+            const double error_limit = lim1 < lim2 ? lim1 : lim2;
+            // kill + per-thread partial sums: total_error, nvalid, GPC sums (compute_next_estimate + gpc_solve)
+            double S[NSUM - 1];
+#pragma unroll
+            for (int q = 0; q < NSUM - 1; q++) S[q] = 0;
+            int nkept = 0;
+#pragma unroll
+            for (int k = 0; k < C; k++) {
+                const int i = k * T + t;
+                if (!(R.sens >> k & 1u)) continue;
+                bool keep = false;
+                if (R.valid >> k & 1u) {
+                    if (R.key[k] > error_limit) {
+                        R.valid &= ~(1u << k);
+                    } else {
+                        keep = true;
+                        nkept++;
+                        S[14] += R.key[k];
+                        const double2 p = s.sensp[i];
+                        const double2 q1 = s.refp[R.cj[k] & 0xffff], q2 = s.refp[R.cj[k] >> 16];
+                        const double px = p.x, py = p.y, qx = q1.x, qy = q1.y;
+                        const double diff0 = q1.x - q2.x, diff1 = q1.y - q2.y;
+                        const double one_on_norm = 1 / sqrt(diff0 * diff0 + diff1 * diff1);
+                        const double ca = +diff1 * one_on_norm, sa = -diff0 * one_on_norm;
+                        const double C00 = ca * ca, C01 = ca * sa, C11 = sa * sa;
+                        S[0] += C00;
+                        S[1] += C01;
+                        S[2] += +px * C00 + py * C01;
+                        S[3] += -py * C00 + px * C01;
+                        S[4] += C11;
+                        S[5] += +px * C01 + py * C11;
+                        S[6] += +px * C11 - py * C01;
+                        S[7] += (px * px) * (+C00) + (px * py) * (+C01 + C01) + (py * py) * (+C11);
+                        S[8] += (px * px) * (+C01) + (px * py) * (-C00 + C11) + (py * py) * (-C01);
+                        S[9] += (px * px) * (+C11) + (px * py) * (-C01 - C01) + (py * py) * (+C00);
+                        S[10] += C00 * qx + C01 * qy;
+                        S[11] += C01 * qx + C11 * qy;
+                        S[12] += qx * (C00 * px + C01 * py) + qy * (C01 * px + C11 * py);
+                        S[13] += qx * (C00 * (-py) + C01 * px) + qy * (C01 * (-py) + C11 * px);
+                    }
+                }
+                s.cj1[i] = keep ? (short)(R.cj[k] & 0xffff) : (short)-1;
+                s.cj2[i] = keep ? (short)(R.cj[k] >> 16) : (short)-1;
+                if (!keep) R.cj[k] = -1;
+            }
+#pragma unroll
+            for (int q = 0; q < NSUM - 1; q++) {
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) S[q] += __shfl_down_sync(0xffffffffu, S[q], o);
+            }
+            if (lane == 0) {
+#pragma unroll
+                for (int q = 0; q < NSUM - 1; q++) s.red[warp * NSUM + q] = S[q];
+            }
+            const int num_after = block_sum<T>(nkept, ctl->ired, 3);  // barrier: publishes red, cj1, cj2
+            // ld_corr_hash of this iteration's correspondences, in parallel
+            {
+                unsigned hc = corr_hash_chunk(s, n, t, a.hash_chunk, a.hashmat);
+                hc = __reduce_xor_sync(0xffffffffu, hc);
+                if (lane == 0 && hc) atomicXor(&ctl->hash_acc[iteration & 1], hc);
+            }
+            if (warp == 0) {
+                double v = 0;
+                if (lane < NSUM - 1)
+                    for (int w = 0; w < NW; w++) v += s.red[w * NSUM + lane];
+                double Tt[NSUM - 1];
+#pragma unroll
+                for (int q = 0; q < NSUM - 1; q++) Tt[q] = __shfl_sync(0xffffffffu, v, q);
+                int st = 0;
+                double xn[3] = {0, 0, 0};
+                if (num_after < fail_perc * n) st = ZHSM_JOB_TOO_FEW_POINTS;
+                else if (!gpc_solve_warp(Tt, xn)) st = ZHSM_JOB_SINGULAR;
+                if (lane == 0) {
+                    ctl->solve_status = st;
+                    ctl->error = Tt[14];
+                    ctl->nvalid = num_after;
+                    if (st == 0) {
+                        const double xo[3] = {x0, x1, x2};
+                        double delta[3];
+                        pose_diff(xn, xo, cs, sn, delta);
+                        const double da = sqrt(delta[0] * delta[0] + delta[1] * delta[1]);
+                        const double db = fabs(delta[2]);
+                        ctl->eps_ok = (da < P.epsilon_xy && db < P.epsilon_theta) ? 1 : 0;
+                        ctl->x[par ^ 1][0] = xn[0];
+                        ctl->x[par ^ 1][1] = xn[1];
+                        ctl->x[par ^ 1][2] = xn[2];
+                        ctl->cs[par ^ 1] = cos(xn[2]);
+                        ctl->sn[par ^ 1] = sin(xn[2]);
+                    }
+                }
+            }
+            __syncthreads();
+            // loop control of icp_loop, evaluated identically by every thread
+            const int st = ctl->solve_status;
+            int brk = 0;
+            if (st) { brk = 2; status = st; }
+            else {
+                newest = par ^ 1;
+                const unsigned h = ctl->hash_acc[iteration & 1] & 0x7FFFFFFFu;
+                bool cyc = false;
+                if (P.use_point_to_line_distance)
+                    for (int q = 0; q < iteration; q++) cyc |= (ctl->hashes[q] == h);
+                if (t == 0) ctl->hashes[iteration] = h;
+                brk = (cyc || ctl->eps_ok) ? 1 : 0;
+            }
+            if (brk == 2) all_ok = 0;
+            if (brk) break;
+            par ^= 1;
+        }
+        // ---- after icp_loop: sm_icp bookkeeping on thread 0 (icp.c)
+        if (t == 0) {
+            const int my_iterations = iteration + 1;
+            const double loop_error = ctl->error;
+            const int loop_valid = ctl->nvalid;
+            int next = 0;
+            n_loops++;
+            if (loop == 0) {
+                iterations = my_iterations;
+                if (!all_ok) { valid = 0; nvalid0 = 0; }
+                else {
+                    valid = 1;
+                    status = ZHSM_JOB_OK;
+                    best_error = loop_error;
+                    nvalid0 = loop_valid;
+                    for (int k = 0; k < 3; k++) { best_x[k] = ctl->x[newest][k]; x_first[k] = best_x[k]; }
+                    if (P.restart && (loop_error / loop_valid) > P.restart_threshold_mean_error) { restarted = 1; next = 1; }
+                }
+            } else {
+                if (!all_ok) { next = 0; status = ZHSM_JOB_OK; }  // a failing restart breaks the restart loop
+                else {
+                    iterations += my_iterations;
+                    if (loop_error < best_error) {
+                        best_error = loop_error;
+                        for (int k = 0; k < 3; k++) best_x[k] = ctl->x[newest][k];
+                    }
+                    next = loop < 6;
+                }
+            }
+            if (next) {
+                const int aidx = loop;  // perturbation of restart number loop+1
+                const double dt = P.restart_dt, dth = P.restart_dtheta;
+                const double pert[6][3] = {{dt, 0, 0}, {-dt, 0, 0}, {0, dt, 0}, {0, -dt, 0}, {0, 0, dth}, {0, 0, -dth}};
+                for (int k = 0; k < 3; k++) ctl->x[0][k] = x_first[k] + pert[aidx][k];
+                ctl->cs[0] = cos(ctl->x[0][2]);
+                ctl->sn[0] = sin(ctl->x[0][2]);
+            }
+            ctl->next = next;
+            ctl->fin = valid | (restarted << 1);
+        }
+        __syncthreads();
+        if (!ctl->next) break;
+    }
+    // ---------------- final correspondences + result record
+    const int fin = ctl->fin;
+    const bool v_ok = fin & 1, v_restarted = fin & 2;
+    __syncthreads();
+    if (v_ok && v_restarted) {
+        // "recompute correspondences in case of restarts" (icp.c): world coords at best x + tricks, no outlier pass
+        if (t == 0) {
+            for (int k = 0; k < 3; k++) ctl->x[0][k] = best_x[k];
+            ctl->cs[0] = cos(best_x[2]);
+            ctl->sn[0] = sin(best_x[2]);
+        }
+        __syncthreads();
+        find_correspondences<T, C>(s, L, n, ctl->x[0][0], ctl->x[0][1], ctl->cs[0], ctl->sn[0], min_theta, C1, maxd2, R);
+    }
+    if (t == 0) ctl->hash_acc[0] = 0;
+#pragma unroll
+    for (int k = 0; k < C; k++) {
+        const int i = k * T + t;
+        if (i >= n) continue;
+        const bool cv = v_ok && (R.valid >> k & 1u);
+        const short j1 = cv ? (short)(R.cj[k] & 0xffff) : (short)-1;
+        const short j2 = cv ? (short)(R.cj[k] >> 16) : (short)-1;
+        s.cj1[i] = j1;
+        s.cj2[i] = j2;
+        if (oj1) { oj1[i] = j1; oj2[i] = j2; }
+    }
+    __syncthreads();
+    {
+        unsigned hc = corr_hash_chunk(s, n, t, a.hash_chunk, a.hashmat);
+        hc = __reduce_xor_sync(0xffffffffu, hc);
+        if (lane == 0 && hc) atomicXor(&ctl->hash_acc[0], hc);
+    }
+    __syncthreads();
+    if (t == 0) {
+        zhsm_result r = {};
+        r.valid = valid;
+        r.status = valid ? ZHSM_JOB_OK : status;
+        r.iterations = iterations;
+        r.n_loops = n_loops;
+        if (valid) {
+            r.x[0] = best_x[0];
+            r.x[1] = best_x[1];
+            r.x[2] = best_x[2];
+            r.error = best_error;
+            r.nvalid = nvalid0;
+            r.corr_hash = ctl->hash_acc[0] & 0x7FFFFFFFu;
+        }
+        *res = r;
+    }
+}
+
+}  // namespace plicp2

@@ -1,0 +1,145 @@
+// laser_slam_b200/csrc/plicp2_search.cuh -- correspondence search of PL-ICP for one sens ray.
+//
+// find_correspondences_tricks (CSM icp_corr_tricks.c) is a SEQUENTIAL algorithm: ray i starts its walk at
+// last_best+1, the j1 of the previous ray that got a valid correspondence, and its jump tables may skip a closer
+// point, so the result depends on where the walk starts (the restatement differs from an exhaustive search on ~1 %
+// of real scan pairs).  The kernel reproduces it exactly: every ray is searched with a SPECULATED last_best
+// (the value the previous iteration saw), then verified against its actual predecessor and re-searched until
+// nothing changes -- the fixpoint is the sequential result (induction over i).
+//
+// The walk itself is restated without libm calls.  CSM stops a direction when
+//     (rho * (dtheta > pi/2 ? 1 : sin(dtheta)))^2 > best_dist,      dtheta = |theta[j] - phi|
+// and rho*|ref_j|*sin(dtheta) is the cross product of the world point with ref point j, so the test becomes
+//     cross^2 > best_dist * |ref_j|^2         (or rho^2 > best_dist when dtheta > pi/2)
+// which needs 4 multiplications instead of a double-precision sin().  `rr < rho` (the jump-table choice) is
+// evaluated on the squares.  Both rewrites change the result only when a comparison is tied to ~1e-16 relative.
+#pragma once
+#include "plicp2_common.cuh"
+
+namespace plicp2 {
+
+struct Ray {
+    double wx, wy;    // ld_compute_world_coords: R(x_old[2]) p + x_old[0:2]
+    double rho2;      // |p_w|^2
+    float phi;        // atan2(wy, wx), float accuracy (only used for the dtheta > pi/2 switch)
+    int start_cell;   // (int)((phi - min_theta) * C1), exact
+};
+
+// world coordinates + start cell of sens ray with sensor-frame point p
+__device__ __forceinline__ Ray make_ray(double2 p, double x0, double x1, double cs, double sn, double min_theta,
+                                        double C1) {
+    Ray r;
+    r.wx = cs * p.x - sn * p.y + x0;
+    r.wy = sn * p.x + cs * p.y + x1;
+    r.rho2 = r.wx * r.wx + r.wy * r.wy;
+    float phf = atan2f((float)r.wy, (float)r.wx);
+    double cell = ((double)phf - min_theta) * C1;
+    // atan2f is good to ~1e-6 rad; when that could move the truncation, decide with the double-precision atan2
+    double fl = floor(cell);
+    double fr = cell - fl;
+    double thr = 2.5e-6 * C1 + 1e-9;
+    if (fr < thr || fr > 1.0 - thr) cell = (atan2(r.wy, r.wx) - min_theta) * C1;
+    r.phi = phf;
+    r.start_cell = (int)cell;  // C truncation (toward zero), like the reference
+    return r;
+}
+
+// One ray's walk.  Returns j1 (a fully valid correspondence) or -1; fills d2 (dist2_j1) and j2.
+static __device__ __noinline__ int tricks_one(const Smem &s, const LaserDev &L, int n, const Ray &r, int last_best,
+                                       double maxd2, double *d2out, int *j2out) {
+    const float HALF_PI_F = 1.57079632679489662f;
+    const int to = n - 1;
+    const double wx = r.wx, wy = r.wy, rho2 = r.rho2;
+    const int start_cell = r.start_cell;
+    int j1 = -1;
+    double best = 42;
+    int we_start_at = (last_best == -1) ? start_cell : last_best + 1;
+    we_start_at = we_start_at > to ? to : we_start_at;
+    we_start_at = we_start_at < 0 ? 0 : we_start_at;
+    int up = we_start_at + 1, down = we_start_at;
+    double last_up = 0, last_down = -1;
+    bool up_stopped = false, down_stopped = false;
+    const short *jt = s.jt;
+    while (!(up_stopped && down_stopped)) {
+        const bool now_up = up_stopped ? false : down_stopped ? true : (last_up < last_down);
+        int idx = now_up ? up : down;
+        if (now_up ? (idx > to) : (idx < 0)) {
+            if (now_up) up_stopped = true; else down_stopped = true;
+            continue;
+        }
+        const double rr2 = s.rr2[idx];
+        int step = now_up ? 1 : -1;
+        bool stop = false;
+        if (rr2 >= 0) {
+            const double2 q = s.refp[idx];
+            const double d = dist2(wx, wy, q.x, q.y);
+            if (now_up) last_up = d; else last_down = d;
+            if (d < best || j1 == -1) { j1 = idx; best = d; }
+            if (now_up ? (idx > start_cell) : (idx < start_cell)) {
+                const float th = theta_f(L, idx);
+                const float dth = now_up ? th - r.phi : r.phi - th;
+                const double cross = wx * q.y - wy * q.x;
+                const bool far = dth > HALF_PI_F;
+                const double lhs = far ? rho2 : cross * cross;
+                const double rhs = far ? best : best * rr2;
+                stop = lhs > rhs;
+                step = jt[((now_up ? 0 : 2) + (rr2 < rho2 ? 0 : 1)) * n + idx];
+            }
+        }
+        if (stop) {
+            if (now_up) up_stopped = true; else down_stopped = true;
+        } else {
+            if (now_up) up = idx + step; else down = idx + step;
+        }
+    }
+    if (j1 == -1 || best > maxd2) return -1;
+    if (j1 == 0 || j1 == n - 1) return -1;
+    int j2up = -1, j2down = -1;
+    for (int j = j1 + 1; j < n; j++) if (s.rr2[j] >= 0) { j2up = j; break; }
+    for (int j = j1 - 1; j >= 0; j--) if (s.rr2[j] >= 0) { j2down = j; break; }
+    if (j2up == -1 && j2down == -1) return -1;
+    int j2;
+    if (j2up == -1) j2 = j2down;
+    else if (j2down == -1) j2 = j2up;
+    else {
+        const double2 qu = s.refp[j2up], qd = s.refp[j2down];
+        j2 = dist2(wx, wy, qu.x, qu.y) < dist2(wx, wy, qd.x, qd.y) ? j2up : j2down;
+    }
+    *d2out = best;
+    *j2out = j2;
+    return j1;
+}
+
+// ld_create_jump_tables(laser_ref) (CSM laser_data.c).  Thread t fills a block of consecutive entries, walking
+// right-to-left (up tables) / left-to-right (down tables) and hopping over already-known runs:
+//   up_bigger[i] = first j>i that is invalid or has r[j] > r[i]; every entry up_bigger[m], final or still at its
+//   initial value 1, only skips points <= r[m], so hopping by it never skips the answer.  Exact, O(n) per table.
+__device__ inline void build_jump_tables(const Smem &s, int n, int t, int nthreads) {
+    volatile short *jt = s.jt;
+    for (int i = t; i < n; i += nthreads) {
+        jt[0 * n + i] = 1; jt[1 * n + i] = 1; jt[2 * n + i] = -1; jt[3 * n + i] = -1;
+    }
+    __syncthreads();
+    const int per = (n + nthreads - 1) / nthreads;
+    const int lo = t * per, hi = (lo + per < n ? lo + per : n);
+    for (int i = hi - 1; i >= lo; i--) {
+        const double ri = s.rr2[i];  // squares are monotone in r >= 0; invalid = -1 like the reading
+        int j = i + 1;
+        while (j < n) { double rj = s.rr2[j]; if (!(rj >= 0 && rj <= ri)) break; j += jt[0 * n + j]; }
+        jt[0 * n + i] = (short)(j - i);
+        j = i + 1;
+        while (j < n) { double rj = s.rr2[j]; if (!(rj >= 0 && rj >= ri)) break; j += jt[1 * n + j]; }
+        jt[1 * n + i] = (short)(j - i);
+    }
+    for (int i = lo; i < hi; i++) {
+        const double ri = s.rr2[i];
+        int j = i - 1;
+        while (j >= 0) { double rj = s.rr2[j]; if (!(rj >= 0 && rj <= ri)) break; j += jt[2 * n + j]; }
+        jt[2 * n + i] = (short)(j - i);
+        j = i - 1;
+        while (j >= 0) { double rj = s.rr2[j]; if (!(rj >= 0 && rj >= ri)) break; j += jt[3 * n + j]; }
+        jt[3 * n + i] = (short)(j - i);
+    }
+}
+
+}  // namespace plicp2

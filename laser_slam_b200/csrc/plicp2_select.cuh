@@ -1,0 +1,133 @@
+// laser_slam_b200/csrc/plicp2_select.cuh -- block-wide helpers: integer sums, exact order statistics, ld_corr_hash.
+#pragma once
+#include "plicp2_common.cuh"
+
+namespace plicp2 {
+
+// Block-wide integer sum, result to every thread, ONE barrier.  `slot` selects one of 4 scratch rows; a row must
+// not be reused until another barrier has passed (callers alternate rows).
+template <int T>
+__device__ __forceinline__ int block_sum(int v, int *ired, int slot) {
+    constexpr int NW = T / 32;
+    int w = __reduce_add_sync(0xffffffffu, v);
+    if ((threadIdx.x & 31) == 0) ired[slot * 16 + (threadIdx.x >> 5)] = w;
+    __syncthreads();
+    int tot = 0;
+#pragma unroll
+    for (int i = 0; i < NW; i++) tot += ired[slot * 16 + i];
+    return tot;
+}
+
+// kill_outliers_trim sorts the distances and reads two order statistics; only the two VALUES are
+// needed, so this is an 8-bit MSD radix select on the bit patterns of the non-negative doubles in keyS[] for both
+// ranks at once.  Per pass: one histogram (both ranks packed in one int: low/high 16 bits), one barrier, then every
+// warp redundantly locates the buckets (no second barrier).  A bucket holding a single key ends that rank early
+// (the key's owner index is remembered next to the histogram); three rotating histogram sets make the zeroing of
+// the next set race-free.
+template <int T, int C>
+__device__ __forceinline__ void select2(const Smem &s, int n, unsigned valid, int rank0, int rank1, double &v0,
+                                        double &v1) {
+    const int t = threadIdx.x, lane = t & 31;
+    const unsigned long long *keyS = s.d2j;
+    unsigned long long prefix[2] = {0, 0};
+    int rem[2] = {rank0, rank1};
+    bool done[2] = {false, false};
+    double val[2] = {0, 0};
+    // set 0 is zeroed by the caller before the barrier that precedes this call
+#pragma unroll 1
+    for (int pass = 0; pass < 8; pass++) {
+        const int shift = 56 - 8 * pass;
+        int *hist = s.hist + 256 * (pass % 3);
+        short *cand = s.candi + 512 * (pass % 3);
+        int *hnext = s.hist + 256 * ((pass + 1) % 3);
+        for (int b = t; b < 256; b += T) hnext[b] = 0;
+#pragma unroll
+        for (int k = 0; k < C; k++) {
+            if (!(valid >> k & 1u)) continue;
+            const int i = k * T + t;
+            const unsigned long long u = keyS[i];
+            const unsigned long long hi = pass == 0 ? 0ull : (u >> (shift + 8));
+            const int digit = (int)((u >> shift) & 255ull);
+            const bool m0 = !done[0] && hi == prefix[0], m1 = !done[1] && hi == prefix[1];
+            if (m0 || m1) atomicAdd(&hist[digit], (m0 ? 1 : 0) | (m1 ? 0x10000 : 0));
+            if (m0) cand[digit] = (short)i;
+            if (m1) cand[256 + digit] = (short)i;
+        }
+        __syncthreads();
+        int loc[8];
+#pragma unroll
+        for (int q = 0; q < 8; q++) loc[q] = hist[lane * 8 + q];
+#pragma unroll
+        for (int r = 0; r < 2; r++) {
+            if (done[r]) continue;
+            int sum = 0;
+#pragma unroll
+            for (int q = 0; q < 8; q++) sum += (loc[q] >> (16 * r)) & 0xffff;
+            int incl = sum;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                int v = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += v;
+            }
+            const int excl = incl - sum;
+            const bool mine = rem[r] >= excl && rem[r] < incl;
+            int bsel = 0, acc = excl, cb = 0;
+            if (mine) {
+                bool found = false;
+#pragma unroll
+                for (int q = 0; q < 8; q++) {
+                    const int c = (loc[q] >> (16 * r)) & 0xffff;
+                    if (!found) {
+                        if (rem[r] < acc + c) { bsel = q; cb = c; found = true; }
+                        else acc += c;
+                    }
+                }
+            }
+            const unsigned who = __ballot_sync(0xffffffffu, mine);
+            const int src = __ffs(who) - 1;  // exactly one lane when the rank is inside the population
+            const int digit = __shfl_sync(0xffffffffu, lane * 8 + bsel, src < 0 ? 0 : src);
+            const int nrem = __shfl_sync(0xffffffffu, rem[r] - acc, src < 0 ? 0 : src);
+            const int cnt = __shfl_sync(0xffffffffu, cb, src < 0 ? 0 : src);
+            prefix[r] = (prefix[r] << 8) | (unsigned long long)digit;
+            rem[r] = nrem;
+            if (cnt == 1 || pass == 7) {
+                done[r] = true;
+                val[r] = pass == 7 ? __longlong_as_double((long long)prefix[r])
+                                   : __longlong_as_double((long long)keyS[cand[256 * r + digit]]);
+            }
+        }
+        if (done[0] && done[1]) break;
+    }
+    v0 = val[0];
+    v1 = val[1];
+}
+
+// ld_corr_hash (CSM laser_data.c) over the stream v_i = j1 + 1000*j2 (or -1):
+//     even i: h ^= (h<<7) ^ v ^ (h>>3)        odd i: h ^= ~((h<<11) ^ v ^ (h>>5))
+// Both steps are affine over GF(2), so the hash of the whole stream is the XOR over chunks of
+// (linear map of the steps that follow the chunk) applied to (the chunk hashed from 0).  Thread t hashes the chunk
+// [t*ch, (t+1)*ch) (ch even) and multiplies by its 32x32 bit matrix hashmat[t] (built on the host by zhsm_set_laser).
+__device__ __forceinline__ unsigned corr_hash_chunk(const Smem &s, int n, int t, int ch, const uint32_t *hashmat) {
+    const int lo = t * ch;
+    if (lo >= n) return 0u;
+    const int hi = lo + ch < n ? lo + ch : n;
+    unsigned h = 0;
+    for (int i = lo; i < hi; i++) {
+        const int j1 = s.cj1[i];
+        const unsigned v = j1 < 0 ? 0xffffffffu : (unsigned)(j1 + 1000 * (int)s.cj2[i]);
+        h ^= ((i & 1) == 0) ? ((h << 7) ^ v ^ (h >> 3)) : (~((h << 11) ^ v ^ (h >> 5)));
+    }
+    const uint4 *m = reinterpret_cast<const uint4 *>(hashmat + 32 * t);
+    unsigned out = 0;
+#pragma unroll
+    for (int q = 0; q < 8; q++) {
+        const uint4 c = __ldg(m + q);
+        out ^= c.x & (0u - ((h >> (4 * q + 0)) & 1u));
+        out ^= c.y & (0u - ((h >> (4 * q + 1)) & 1u));
+        out ^= c.z & (0u - ((h >> (4 * q + 2)) & 1u));
+        out ^= c.w & (0u - ((h >> (4 * q + 3)) & 1u));
+    }
+    return out;
+}
+
+}  // namespace plicp2

@@ -141,9 +141,53 @@ extern "C" zhsm_status zhsm_set_laser(zhsm_handle *h, const zhsm_laser *laser) {
     if (h->d_cs) { cudaFree(h->d_cs); h->d_cs = nullptr; }
     ZHSM_CUDA_TRY(h, cudaMalloc(&h->d_cs, sizeof(double2) * n));
     ZHSM_CUDA_TRY(h, cudaMemcpy(h->d_cs, cs.data(), sizeof(double2) * n, cudaMemcpyHostToDevice));
+    // GF(2) matrices of the parallel ld_corr_hash for this beam count / CTA shape
+    {
+        int T, C, ch;
+        plicp_shape(n, &T, &C, &ch);
+        if (C < 0) { h->err = "no PL-ICP kernel instance for this beam count"; return ZHSM_ERR_UNSUPPORTED; }
+        std::vector<uint32_t> mat;
+        plicp_build_hash_matrices(n, T, ch, mat);
+        if (h->d_hashmat) { cudaFree(h->d_hashmat); h->d_hashmat = nullptr; }
+        ZHSM_CUDA_TRY(h, cudaMalloc(&h->d_hashmat, sizeof(uint32_t) * mat.size()));
+        ZHSM_CUDA_TRY(h, cudaMemcpy(h->d_hashmat, mat.data(), sizeof(uint32_t) * mat.size(), cudaMemcpyHostToDevice));
+        h->hash_chunk = ch;
+    }
     h->laser = *laser;
     h->have_laser = true;
     return ZHSM_OK;
+}
+
+// Host emulation of the kernel's chunked ld_corr_hash (test hook: the same matrices, chunking and XOR combine as
+// plicp2_select.cuh::corr_hash_chunk, no device needed).  seq = the sequential CSM hash, par = the chunked one.
+extern "C" int zhsm_debug_corr_hash(const int32_t *stream, int n, uint32_t *seq, uint32_t *par) {
+    if (!stream || n < 1 || n > ZHSM_MAX_BEAMS || !seq || !par) return 1;
+    int T, C, ch;
+    plicp_shape(n, &T, &C, &ch);
+    if (C < 0) return 2;
+    std::vector<uint32_t> mat;
+    plicp_build_hash_matrices(n, T, ch, mat);
+    uint32_t h = 0;
+    for (int i = 0; i < n; i++) {
+        uint32_t v = (uint32_t)stream[i];
+        h ^= ((i & 1) == 0) ? ((h << 7) ^ v ^ (h >> 3)) : (~((h << 11) ^ v ^ (h >> 5)));
+    }
+    *seq = h & 0x7FFFFFFFu;
+    uint32_t acc = 0;
+    for (int t = 0; t < T; t++) {
+        int lo = t * ch, hi = lo + ch < n ? lo + ch : n;
+        if (lo >= n) break;
+        uint32_t c = 0;
+        for (int i = lo; i < hi; i++) {
+            uint32_t v = (uint32_t)stream[i];
+            c ^= ((i & 1) == 0) ? ((c << 7) ^ v ^ (c >> 3)) : (~((c << 11) ^ v ^ (c >> 5)));
+        }
+        uint32_t out = 0;
+        for (int b = 0; b < 32; b++) if (c >> b & 1u) out ^= mat[(size_t)t * 32 + b];
+        acc ^= out;
+    }
+    *par = acc & 0x7FFFFFFFu;
+    return 0;
 }
 
 // CCanonicalMatcher::sm_init (src/zhcsm/ZHCanonical_Matcher.cpp:83-157)
@@ -231,6 +275,7 @@ extern "C" zhsm_status zhsm_plicp_batch(zhsm_handle *h, const float *scans, int 
     a.L.min_valid_points = h->laser.min_valid_points; a.L.scan_window = h->laser.scan_window;
     a.cs = h->d_cs;
     a.hashmat = h->d_hashmat;
+    a.hash_chunk = h->hash_chunk;
 
     // ld_valid_fields' per-scan-geometry checks (laser_data.c): nrays, fov, theta[] consistent by construction
     {

@@ -47,13 +47,17 @@ struct PlicpArgs {
     zhsm_result *results;    // [B]
     int16_t *corr_j1, *corr_j2; // [B][n] or null
     const double2 *cs;       // [n]
-    const uint32_t *hashmat;
+    const uint32_t *hashmat; // [T][32] GF(2) matrices of the parallel ld_corr_hash (plicp2_select.cuh)
+    int hash_chunk;          // stream elements hashed per thread (even)
     int B;
     LaserDev L;
     zhsm_plicp_params P;
 };
 
 cudaError_t plicp_launch(const PlicpArgs &a, int sm_count, cudaStream_t st, int *launched);
+// CTA shape the PL-ICP kernel uses for n beams: T threads, C rays per thread, hash chunk (even) per thread
+void plicp_shape(int n, int *T, int *C, int *hash_chunk);
+void plicp_build_hash_matrices(int n, int T, int ch, std::vector<uint32_t> &mat);
 cudaError_t median_filter_launch(float *scans, int S, int n, cudaStream_t st);
 
 #define ZHSM_CUDA_TRY(h, expr)                                                              \
