@@ -1,8 +1,12 @@
 // laser_slam_b200/csrc/plicp2_common.cuh -- shared-memory layout and small device helpers of the PL-ICP kernel.
 //
 // One CTA of T threads owns one job (ref scan, sens scan, first guess).  Thread t owns the sens rays
-// i = k*T + t (k < C): the 32 lanes of a warp work on 32 neighbouring rays, so their searches touch
+// i = k*T + t (k < C = ceil(n/T)): the 32 lanes of a warp work on 32 neighbouring rays, so their searches touch
 // neighbouring ref points (conflict-free shared-memory reads) and take similar numbers of steps.
+//
+// Everything a job needs lives in dynamic shared memory, addressed as byte offsets from the extern array so that
+// every access, also inside non-inlined device functions, compiles to LDS/STS (a generic pointer costs a long
+// scoreboard stall per load).
 #pragma once
 #include <cuda_runtime.h>
 #include <math.h>
@@ -28,55 +32,53 @@ struct Ctl {
     int fin;            // valid | restarted<<1
 };
 
-struct Smem {
-    double2 *refp;             // [n] ref points ("world" frame = ref sensor frame); NaN when invalid
-    double2 *sensp;            // [n] sens points, sens sensor frame; x = NaN when invalid
-    double *rr2;               // [n] squared ref reading [m^2], -1 when invalid
-    unsigned long long *d2j;   // [n] min dist2 per ref index (kill_outliers_double); then the trim keys per sens ray
-    double *red;               // [nwarps][NSUM]
-    Ctl *ctl;
-    int *hist;                 // [3][256] radix-select histograms (both ranks packed 16:16)
-    short *candi;              // [3][2][256] radix-select: a ray index per bucket
-    short *cj1, *cj2;          // [n] current correspondences (-1 none): fixpoint exchange, hash stream, output
-    short *jt;                 // [4][n] up_bigger, up_smaller, down_bigger, down_smaller
+// byte offsets into the dynamic shared memory block
+struct Lay {
+    unsigned refp;   // double2[n] ref points ("world" frame = ref sensor frame); NaN when invalid
+    unsigned sensp;  // double2[n] sens points, sens sensor frame; x = NaN when invalid
+    unsigned rr2;    // double[n]  squared ref reading [m^2], -1 when invalid
+    unsigned d2j;    // u64[n]     min dist2 per ref index (kill_outliers_double); then the trim keys per sens ray
+    unsigned red;    // double[nwarps][NSUM]
+    unsigned ctl;    // Ctl
+    unsigned hist;   // int[3][256]   radix-select histograms (both ranks packed 16:16)
+    unsigned candi;  // short[3][2][256] radix-select: a ray index per bucket
+    unsigned cj1;    // short[n] current correspondences (-1 none): fixpoint exchange, hash stream, output
+    unsigned cj2;    // short[n]
+    unsigned spec;   // short[n] last_best each ray was (or will be) searched with
+    unsigned jt;     // short[4][n] up_bigger, up_smaller, down_bigger, down_smaller
+    unsigned total;
 };
 
-__host__ __device__ inline size_t align16(size_t b) { return (b + 15) & ~(size_t)15; }
+__host__ __device__ inline unsigned align16(unsigned b) { return (b + 15u) & ~15u; }
 
-__host__ __device__ inline size_t smem_bytes(int n, int nthreads) {
-    size_t nw = (nthreads + 31) / 32;
-    size_t b = 0;
-    b += sizeof(double2) * n * 2;         // refp, sensp
-    b += sizeof(double) * n * 2;          // rr2, d2j
-    b += sizeof(double) * nw * NSUM;      // red
-    b += align16(sizeof(Ctl));
-    b += sizeof(int) * 768;               // hist
-    b += sizeof(short) * 1536;            // candi
-    b += align16(sizeof(short) * n) * 2;  // cj1, cj2
-    b += align16(sizeof(short) * 4 * n);  // jt
-    return align16(b);
+__host__ __device__ inline Lay make_layout(int n, int nthreads) {
+    const unsigned nw = (unsigned)(nthreads + 31) / 32, un = (unsigned)n;
+    Lay l;
+    unsigned o = 0;
+    l.refp = o;  o += 16u * un;
+    l.sensp = o; o += 16u * un;
+    l.rr2 = o;   o += 8u * un;
+    l.d2j = o;   o += 8u * un;
+    l.red = o;   o += 8u * nw * NSUM;
+    l.ctl = o;   o += align16((unsigned)sizeof(Ctl));
+    l.hist = o;  o += 4u * 768;
+    l.candi = o; o += 2u * 1536;
+    l.cj1 = o;   o += align16(2u * un);
+    l.cj2 = o;   o += align16(2u * un);
+    l.spec = o;  o += align16(2u * un);
+    l.jt = o;    o += align16(8u * un);
+    l.total = align16(o);
+    return l;
 }
 
-__device__ inline Smem carve(unsigned char *p, int n, int nthreads) {
-    int nw = (nthreads + 31) / 32;
-    Smem s;
-    s.refp = (double2 *)p;  p += sizeof(double2) * n;
-    s.sensp = (double2 *)p; p += sizeof(double2) * n;
-    s.rr2 = (double *)p;    p += sizeof(double) * n;
-    s.d2j = (unsigned long long *)p; p += sizeof(unsigned long long) * n;
-    s.red = (double *)p;    p += sizeof(double) * nw * NSUM;
-    s.ctl = (Ctl *)p;       p += align16(sizeof(Ctl));
-    s.hist = (int *)p;      p += sizeof(int) * 768;
-    s.candi = (short *)p;   p += sizeof(short) * 1536;
-    s.cj1 = (short *)p;     p += align16(sizeof(short) * n);
-    s.cj2 = (short *)p;     p += align16(sizeof(short) * n);
-    s.jt = (short *)p;
-    return s;
-}
+__host__ __device__ inline size_t smem_bytes(int n, int nthreads) { return make_layout(n, nthreads).total; }
+
+extern __shared__ __align__(16) unsigned char smem_raw[];
+#define PL_SH(type, off) (reinterpret_cast<type *>(smem_raw + (off)))
 
 // theta[j] exactly as fromPMScan2LDP builds it (src/zhcsm/ZHCanonical_Matcher.cpp:210): float fi_min + float dfi*j
-__device__ __forceinline__ float theta_f(const LaserDev &L, int j) {
-    return __fadd_rn(L.fi_min, __fmul_rn(L.dfi, (float)(unsigned)j));
+__device__ __forceinline__ float theta_f(float fi_min, float dfi, int j) {
+    return __fadd_rn(fi_min, __fmul_rn(dfi, (float)(unsigned)j));
 }
 
 __device__ __forceinline__ double dist2(double ax, double ay, double bx, double by) {

@@ -1,26 +1,26 @@
 // laser_slam_b200/csrc/plicp2_dispatch.cu -- host side of the PL-ICP kernel: CTA shape per beam count, the GF(2)
 // matrices of the parallel ld_corr_hash, and the launch dispatch over the compiled instances.
+#include <stdlib.h>
+
 #include <vector>
 
 #include "zhsm_internal.h"
 
-cudaError_t plicp_launch_t128(const PlicpArgs &a, int C, cudaStream_t st);
-cudaError_t plicp_launch_t256(const PlicpArgs &a, int C, cudaStream_t st);
-cudaError_t plicp_launch_t512(const PlicpArgs &a, int C, cudaStream_t st);
+cudaError_t plicp_launch_t128(const PlicpArgs &a, cudaStream_t st);
+cudaError_t plicp_launch_t256(const PlicpArgs &a, cudaStream_t st);
+cudaError_t plicp_launch_t512(const PlicpArgs &a, cudaStream_t st);
 
-static int round_up_to(int c, const int *opts, int nopts) {
-    for (int i = 0; i < nopts; i++) if (c <= opts[i]) return opts[i];
-    return -1;
-}
-
+// CTA size per beam count: enough threads that a thread owns <= ~5 rays, and as many resident CTAs per SM as the
+// shared-memory footprint (~68 B per beam) allows.  ZHSM_PLICP_T overrides (tuning only).
 void plicp_shape(int n, int *T, int *C, int *hash_chunk) {
-    static const int c128[] = {2, 3, 5, 7, 9}, c256[] = {5, 7, 9}, c512[] = {6, 8};
-    int t, c;
-    if (n <= 128 * 9) { t = 128; c = round_up_to((n + t - 1) / t, c128, 5); }
-    else if (n <= 256 * 9) { t = 256; c = round_up_to((n + t - 1) / t, c256, 3); }
-    else { t = 512; c = round_up_to((n + t - 1) / t, c512, 2); }
+    int t = n <= 640 ? 128 : (n <= 1536 ? 256 : 512);
+    if (const char *e = getenv("ZHSM_PLICP_T")) {
+        int v = atoi(e);
+        if (v == 128 || v == 256 || v == 512) t = v;
+    }
+    while ((n + t - 1) / t > 32 && t < 512) t *= 2;
     *T = t;
-    *C = c;
+    *C = (n + t - 1) / t;
     int ch = (n + t - 1) / t;
     if (ch & 1) ch++;
     *hash_chunk = ch;
@@ -47,8 +47,8 @@ cudaError_t plicp_launch(const PlicpArgs &a, int sm_count, cudaStream_t st, int 
     (void)sm_count;
     int T, C, ch;
     plicp_shape(a.L.n, &T, &C, &ch);
-    if (C < 0 || ch != a.hash_chunk) return cudaErrorInvalidValue;
-    cudaError_t e = T == 128 ? plicp_launch_t128(a, C, st) : T == 256 ? plicp_launch_t256(a, C, st) : plicp_launch_t512(a, C, st);
+    if (C > 32 || ch != a.hash_chunk) return cudaErrorInvalidValue;
+    cudaError_t e = T == 128 ? plicp_launch_t128(a, st) : T == 256 ? plicp_launch_t256(a, st) : plicp_launch_t512(a, st);
     if (e == cudaSuccess && launched) *launched += 1;
     return e;
 }

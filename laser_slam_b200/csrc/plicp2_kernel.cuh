@@ -9,102 +9,99 @@
 
 namespace plicp2 {
 
-// Per-thread state of its C rays i = k*T + t.
-template <int C>
-struct Rays {
-    int cj[C];      // j1 | j2 << 16 of the current correspondence (valid bit set) else -1
-    int spec[C];    // last_best this ray was (or will be) searched with
-    double key[C];  // dist2_j1 after the search, then the trim distance
-    unsigned valid; // bit k: ray k has a correspondence
-    unsigned sens;  // bit k: sens ray k exists and is valid
+// pose of the current iteration + what make_ray needs
+struct IterCtx {
+    double x0, x1, cs, sn;
+    double min_theta, C1;
 };
 
-template <int T, int C>
-__device__ __forceinline__ void search_ray(const Smem &s, const LaserDev &L, int n, int k, int i, double x0,
-                                           double x1, double cs, double sn, double min_theta, double C1,
-                                           double maxd2, Rays<C> &R) {
-    const Ray ray = make_ray(s.sensp[i], x0, x1, cs, sn, min_theta, C1);
-    double d2 = 0;
-    int j2 = 0;
-    const int j1 = tricks_one(s, L, n, ray, R.spec[k], maxd2, &d2, &j2);
-    if (j1 >= 0) {
-        R.cj[k] = j1 | (j2 << 16);
-        R.key[k] = d2;
-        R.valid |= 1u << k;
-    } else {
-        R.cj[k] = -1;
-        R.valid &= ~(1u << k);
-    }
-    s.cj1[i] = (short)j1;
+// search sens ray i with its speculated last_best; returns true when it got a correspondence
+__device__ __forceinline__ bool search_ray(const Lay &l, const WalkCtx &w, const IterCtx &it, int i) {
+    const Ray ray = make_ray(PL_SH(const double2, l.sensp)[i], it.x0, it.x1, it.cs, it.sn, it.min_theta, it.C1);
+    int j2 = -1;
+    const int j1 = tricks_one(w, ray, (int)PL_SH(const short, l.spec)[i], &j2);
+    PL_SH(short, l.cj1)[i] = (short)j1;
+    PL_SH(short, l.cj2)[i] = (short)(j1 >= 0 ? j2 : -1);
+    return j1 >= 0;
 }
 
 // find_correspondences_tricks for the whole scan: speculate / verify / re-search until the sequential result.
-template <int T, int C>
-__device__ __forceinline__ void find_correspondences(const Smem &s, const LaserDev &L, int n, double x0, double x1,
-                                                     double cs, double sn, double min_theta, double C1,
-                                                     double maxd2, Rays<C> &R) {
+// sens: bit k = ray k*T+t exists and is valid; returns the mask of rays holding a correspondence.
+template <int T>
+__device__ __forceinline__ unsigned find_correspondences(const Lay &l, const WalkCtx &w, const IterCtx &it, int C,
+                                                         unsigned sens) {
     const int t = threadIdx.x;
-#pragma unroll
+    unsigned valid = 0;
+#pragma unroll 1
     for (int k = 0; k < C; k++)
-        if (R.sens >> k & 1u) search_ray<T, C>(s, L, n, k, k * T + t, x0, x1, cs, sn, min_theta, C1, maxd2, R);
+        if (sens >> k & 1u)
+            if (search_ray(l, w, it, k * T + t)) valid |= 1u << k;
     __syncthreads();
+    const short *cj1 = PL_SH(const short, l.cj1);
+    short *spec = PL_SH(short, l.spec);
     while (true) {
         unsigned need = 0;
-#pragma unroll
+#pragma unroll 1
         for (int k = 0; k < C; k++) {
-            if (!(R.sens >> k & 1u)) continue;
+            if (!(sens >> k & 1u)) continue;
+            const int i = k * T + t;
             int actual = -1;
-            for (int u = k * T + t - 1; u >= 0; u--) {
-                const int v = s.cj1[u];
+            for (int u = i - 1; u >= 0; u--) {
+                const int v = cj1[u];
                 if (v >= 0) { actual = v; break; }
             }
-            if (actual != R.spec[k]) { need |= 1u << k; R.spec[k] = actual; }
+            if (actual != (int)spec[i]) { need |= 1u << k; spec[i] = (short)actual; }
         }
         if (!__syncthreads_or((int)need)) break;
-#pragma unroll
+#pragma unroll 1
         for (int k = 0; k < C; k++)
-            if (need >> k & 1u) search_ray<T, C>(s, L, n, k, k * T + t, x0, x1, cs, sn, min_theta, C1, maxd2, R);
+            if (need >> k & 1u) {
+                if (search_ray(l, w, it, k * T + t)) valid |= 1u << k;
+                else valid &= ~(1u << k);
+            }
         __syncthreads();
     }
+    return valid;
 }
 
-template <int T, int C>
-__global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 2 : 1))) plicp2_kernel(PlicpArgs a) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
+template <int T>
+__global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2_kernel(PlicpArgs a) {
     constexpr int NW = T / 32;
     const int n = a.L.n;
+    const int C = (n + T - 1) / T;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int job = blockIdx.x;
-    const Smem s = carve(smem_raw, n, T);
-    Ctl *ctl = s.ctl;
+    const Lay l = make_layout(n, T);
+    Ctl *ctl = PL_SH(Ctl, l.ctl);
     const LaserDev L = a.L;
     const zhsm_plicp_params &P = a.P;
+    double2 *refp = PL_SH(double2, l.refp), *sensp = PL_SH(double2, l.sensp);
+    double *rr2a = PL_SH(double, l.rr2);
+    unsigned long long *d2j = PL_SH(unsigned long long, l.d2j);
+    short *cj1 = PL_SH(short, l.cj1), *cj2 = PL_SH(short, l.cj2);
+    double *red = PL_SH(double, l.red);
 
     // ---------------- load + fromPMScan2LDP + ld_valid_fields + ld_invalid_if_outside + ld_compute_cartesian
     const float *ref_row = a.scans + (size_t)a.ref_idx[job] * n;
     const float *sens_row = a.scans + (size_t)a.sens_idx[job] * n;
     int bad_field = 0, nvf_ref = 0, nvf_sens = 0;
-    Rays<C> R;
-    R.valid = 0;
-    R.sens = 0;
-#pragma unroll
+    unsigned sens = 0;
+#pragma unroll 1
     for (int k = 0; k < C; k++) {
-        R.cj[k] = -1;
-        R.spec[k] = -1;
-        R.key[k] = 0;
         const int i = k * T + t;
-        if (i >= n) continue;
+        if (i >= n) break;
         const double2 cs = a.cs[i];
         double rr = reading_of(__ldg(ref_row + i), L, P, &bad_field);
         nvf_ref += (rr != -1.0);
-        s.rr2[i] = rr >= 0 ? rr * rr : -1.0;
-        s.refp[i] = rr >= 0 ? make_double2(cs.x * rr, cs.y * rr) : make_double2(nan(""), nan(""));
+        rr2a[i] = rr >= 0 ? rr * rr : -1.0;
+        refp[i] = rr >= 0 ? make_double2(cs.x * rr, cs.y * rr) : make_double2(nan(""), nan(""));
         double rs = reading_of(__ldg(sens_row + i), L, P, &bad_field);
         nvf_sens += (rs != -1.0);
-        s.sensp[i] = rs >= 0 ? make_double2(cs.x * rs, cs.y * rs) : make_double2(nan(""), nan(""));
-        if (rs >= 0) R.sens |= 1u << k;
-        s.cj1[i] = -1;
-        s.cj2[i] = -1;
+        sensp[i] = rs >= 0 ? make_double2(cs.x * rs, cs.y * rs) : make_double2(nan(""), nan(""));
+        if (rs >= 0) sens |= 1u << k;
+        cj1[i] = -1;
+        cj2[i] = -1;
+        PL_SH(short, l.spec)[i] = -1;
     }
     if (t == 0) {
         for (int k = 0; k < 3; k++) ctl->x[0][k] = a.first_guess ? a.first_guess[3 * (size_t)job + k] : 0.0;
@@ -130,59 +127,77 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 2 : 1))) plicp2
         if (oj1) for (int i = t; i < n; i += T) { oj1[i] = -1; oj2[i] = -1; }
         return;
     }
-    build_jump_tables(s, n, t, T);
+    build_jump_tables(l, n, t, T);
     __syncthreads();
 
-    const double min_theta = (double)theta_f(L, 0), max_theta = (double)theta_f(L, n - 1);
-    const double C1 = (double)n / (max_theta - min_theta);
-    const double maxd2 = P.max_correspondence_dist * P.max_correspondence_dist;
+    IterCtx it;
+    it.min_theta = (double)theta_f(L.fi_min, L.dfi, 0);
+    it.C1 = (double)n / ((double)theta_f(L.fi_min, L.dfi, n - 1) - it.min_theta);
+    WalkCtx wc;
+    wc.refp = l.refp; wc.rr2 = l.rr2; wc.jt = l.jt; wc.n = n; wc.fi_min = L.fi_min; wc.dfi = L.dfi;
+    wc.maxd2 = P.max_correspondence_dist * P.max_correspondence_dist;
     const int max_it = P.max_iterations < ZHSM_MAX_ITER ? P.max_iterations : ZHSM_MAX_ITER;
     const double fail_perc = 0.05;
     const unsigned long long BIG = (unsigned long long)__double_as_longlong(1000000.0);
 
     // sm_icp bookkeeping (icp.c), meaningful on thread 0
     double best_x[3] = {0, 0, 0}, x_first[3] = {0, 0, 0}, best_error = 0;
-    int iterations = 0, nvalid0 = 0, n_loops = 0, restarted = 0, valid = 0, status = ZHSM_JOB_OK;
+    int iterations = 0, nvalid0 = 0, n_loops = 0, restarted = 0, valid_out = 0, status = ZHSM_JOB_OK;
+    unsigned valid = 0;
 
     for (int loop = 0; loop < 7; loop++) {
         int iteration = 0, all_ok = 1, par = 0, newest = 0;
         for (iteration = 0; iteration < max_it; iteration++) {
-            const double x0 = ctl->x[par][0], x1 = ctl->x[par][1], x2 = ctl->x[par][2];
-            const double cs = ctl->cs[par], sn = ctl->sn[par];
-            for (int j = t; j < n; j += T) s.d2j[j] = BIG;
+            it.x0 = ctl->x[par][0];
+            it.x1 = ctl->x[par][1];
+            it.cs = ctl->cs[par];
+            it.sn = ctl->sn[par];
+            for (int j = t; j < n; j += T) d2j[j] = BIG;
             if (t == 0) ctl->hash_acc[iteration & 1] = 0;
-            find_correspondences<T, C>(s, L, n, x0, x1, cs, sn, min_theta, C1, maxd2, R);
-            // kill_outliers_double (icp_outliers.c): min dist2 per ref index
+            valid = find_correspondences<T>(l, wc, it, C, sens);
+            // kill_outliers_double (icp_outliers.c): min dist2_j1 per ref index.  dist2_j1 is recomputed
+            // from the same operands the walk used (bit-identical), so it needs no storage.
             if (P.outliers_remove_doubles) {
-#pragma unroll
-                for (int k = 0; k < C; k++)
-                    if (R.valid >> k & 1u)
-                        atomicMin(&s.d2j[R.cj[k] & 0xffff], (unsigned long long)__double_as_longlong(R.key[k]));
+#pragma unroll 1
+                for (int k = 0; k < C; k++) {
+                    if (!(valid >> k & 1u)) continue;
+                    const int i = k * T + t;
+                    const double2 p = sensp[i];
+                    const double wx = it.cs * p.x - it.sn * p.y + it.x0;
+                    const double wy = it.sn * p.x + it.cs * p.y + it.x1;
+                    const int j1 = cj1[i];
+                    const double2 q = refp[j1];
+                    atomicMin(&d2j[j1], (unsigned long long)__double_as_longlong(dist2(wx, wy, q.x, q.y)));
+                }
             }
-            const int num_corr = block_sum<T>(__popc(R.valid), ctl->ired, 1);
+            const int num_corr = block_sum<T>(__popc(valid), ctl->ired, 1);
             if (num_corr < fail_perc * n) { all_ok = 0; status = ZHSM_JOB_TOO_FEW_POINTS; break; }
             if (P.outliers_remove_doubles) {
-#pragma unroll
-                for (int k = 0; k < C; k++)
-                    if (R.valid >> k & 1u) {
-                        const double dj = __longlong_as_double((long long)s.d2j[R.cj[k] & 0xffff]);
-                        if (R.key[k] > (3.0 * 3.0) * dj) R.valid &= ~(1u << k);
-                    }
+#pragma unroll 1
+                for (int k = 0; k < C; k++) {
+                    if (!(valid >> k & 1u)) continue;
+                    const int i = k * T + t;
+                    const double2 p = sensp[i];
+                    const double wx = it.cs * p.x - it.sn * p.y + it.x0;
+                    const double wy = it.sn * p.x + it.cs * p.y + it.x1;
+                    const int j1 = cj1[i];
+                    const double2 q = refp[j1];
+                    const double dj = __longlong_as_double((long long)d2j[j1]);
+                    if (dist2(wx, wy, q.x, q.y) > (3.0 * 3.0) * dj) valid &= ~(1u << k);
+                }
             }
-            for (int b = t; b < 256; b += T) s.hist[b] = 0;
-            const int kcnt = block_sum<T>(__popc(R.valid), ctl->ired, 2);  // all reads of d2j are done
+            for (int b = t; b < 256; b += T) PL_SH(int, l.hist)[b] = 0;
+            const int kcnt = block_sum<T>(__popc(valid), ctl->ired, 2);  // all reads of d2j are done
             // kill_outliers_trim: distance to the segment (j1,j2); keys go to shared memory
-#pragma unroll
+#pragma unroll 1
             for (int k = 0; k < C; k++) {
-                if (!(R.valid >> k & 1u)) continue;
+                if (!(valid >> k & 1u)) continue;
                 const int i = k * T + t;
-                const double2 p = s.sensp[i];
-                const double wx = cs * p.x - sn * p.y + x0;
-                const double wy = sn * p.x + cs * p.y + x1;
-                const double2 q1 = s.refp[R.cj[k] & 0xffff], q2 = s.refp[R.cj[k] >> 16];
-                const double d = dist_to_segment(q1.x, q1.y, q2.x, q2.y, wx, wy);
-                R.key[k] = d;
-                s.d2j[i] = (unsigned long long)__double_as_longlong(d);
+                const double2 p = sensp[i];
+                const double wx = it.cs * p.x - it.sn * p.y + it.x0;
+                const double wy = it.sn * p.x + it.cs * p.y + it.x1;
+                const double2 q1 = refp[cj1[i]], q2 = refp[cj2[i]];
+                d2j[i] = (unsigned long long)__double_as_longlong(dist_to_segment(q1.x, q1.y, q2.x, q2.y, wx, wy));
             }
             int order = (int)floor(kcnt * P.outliers_maxPerc);
             order = order < kcnt - 1 ? order : kcnt - 1;
@@ -191,7 +206,7 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 2 : 1))) plicp2
             order2 = order2 < kcnt - 1 ? order2 : kcnt - 1;
             order2 = order2 > 0 ? order2 : 0;
             double lim1, d_o2;
-            select2<T, C>(s, n, R.valid, order, order2, lim1, d_o2);
+            select2<T>(l, C, valid, order, order2, lim1, d_o2);
             const double lim2 = P.outliers_adaptive_mult * d_o2;
             const double error_limit = lim1 < lim2 ? lim1 : lim2;
             // kill + per-thread partial sums: total_error, nvalid, GPC sums (compute_next_estimate + gpc_solve)
@@ -199,20 +214,21 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 2 : 1))) plicp2
 #pragma unroll
             for (int q = 0; q < NSUM - 1; q++) S[q] = 0;
             int nkept = 0;
-#pragma unroll
+#pragma unroll 1
             for (int k = 0; k < C; k++) {
+                if (!(sens >> k & 1u)) continue;
                 const int i = k * T + t;
-                if (!(R.sens >> k & 1u)) continue;
                 bool keep = false;
-                if (R.valid >> k & 1u) {
-                    if (R.key[k] > error_limit) {
-                        R.valid &= ~(1u << k);
+                if (valid >> k & 1u) {
+                    const double key = __longlong_as_double((long long)d2j[i]);
+                    if (key > error_limit) {
+                        valid &= ~(1u << k);
                     } else {
                         keep = true;
                         nkept++;
-                        S[14] += R.key[k];
-                        const double2 p = s.sensp[i];
-                        const double2 q1 = s.refp[R.cj[k] & 0xffff], q2 = s.refp[R.cj[k] >> 16];
+                        S[14] += key;
+                        const double2 p = sensp[i];
+                        const double2 q1 = refp[cj1[i]], q2 = refp[cj2[i]];
                         const double px = p.x, py = p.y, qx = q1.x, qy = q1.y;
                         const double diff0 = q1.x - q2.x, diff1 = q1.y - q2.y;
                         const double one_on_norm = 1 / sqrt(diff0 * diff0 + diff1 * diff1);
@@ -234,9 +250,7 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 2 : 1))) plicp2
                         S[13] += qx * (C00 * (-py) + C01 * px) + qy * (C01 * (-py) + C11 * px);
                     }
                 }
-                s.cj1[i] = keep ? (short)(R.cj[k] & 0xffff) : (short)-1;
-                s.cj2[i] = keep ? (short)(R.cj[k] >> 16) : (short)-1;
-                if (!keep) R.cj[k] = -1;
+                if (!keep) { cj1[i] = -1; cj2[i] = -1; }
             }
 #pragma unroll
             for (int q = 0; q < NSUM - 1; q++) {
@@ -245,19 +259,19 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 2 : 1))) plicp2
             }
             if (lane == 0) {
 #pragma unroll
-                for (int q = 0; q < NSUM - 1; q++) s.red[warp * NSUM + q] = S[q];
+                for (int q = 0; q < NSUM - 1; q++) red[warp * NSUM + q] = S[q];
             }
             const int num_after = block_sum<T>(nkept, ctl->ired, 3);  // barrier: publishes red, cj1, cj2
             // ld_corr_hash of this iteration's correspondences, in parallel
             {
-                unsigned hc = corr_hash_chunk(s, n, t, a.hash_chunk, a.hashmat);
+                unsigned hc = corr_hash_chunk(l, n, t, a.hash_chunk, a.hashmat);
                 hc = __reduce_xor_sync(0xffffffffu, hc);
                 if (lane == 0 && hc) atomicXor(&ctl->hash_acc[iteration & 1], hc);
             }
             if (warp == 0) {
                 double v = 0;
                 if (lane < NSUM - 1)
-                    for (int w = 0; w < NW; w++) v += s.red[w * NSUM + lane];
+                    for (int w = 0; w < NW; w++) v += red[w * NSUM + lane];
                 double Tt[NSUM - 1];
 #pragma unroll
                 for (int q = 0; q < NSUM - 1; q++) Tt[q] = __shfl_sync(0xffffffffu, v, q);
@@ -270,9 +284,9 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 2 : 1))) plicp2
                     ctl->error = Tt[14];
                     ctl->nvalid = num_after;
                     if (st == 0) {
-                        const double xo[3] = {x0, x1, x2};
+                        const double xo[3] = {it.x0, it.x1, ctl->x[par][2]};
                         double delta[3];
-                        pose_diff(xn, xo, cs, sn, delta);
+                        pose_diff(xn, xo, it.cs, it.sn, delta);
                         const double da = sqrt(delta[0] * delta[0] + delta[1] * delta[1]);
                         const double db = fabs(delta[2]);
                         ctl->eps_ok = (da < P.epsilon_xy && db < P.epsilon_theta) ? 1 : 0;
@@ -311,9 +325,9 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 2 : 1))) plicp2
             n_loops++;
             if (loop == 0) {
                 iterations = my_iterations;
-                if (!all_ok) { valid = 0; nvalid0 = 0; }
+                if (!all_ok) { valid_out = 0; nvalid0 = 0; }
                 else {
-                    valid = 1;
+                    valid_out = 1;
                     status = ZHSM_JOB_OK;
                     best_error = loop_error;
                     nvalid0 = loop_valid;
@@ -340,7 +354,7 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 2 : 1))) plicp2
                 ctl->sn[0] = sin(ctl->x[0][2]);
             }
             ctl->next = next;
-            ctl->fin = valid | (restarted << 1);
+            ctl->fin = valid_out | (restarted << 1);
         }
         __syncthreads();
         if (!ctl->next) break;
@@ -357,34 +371,35 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 2 : 1))) plicp2
             ctl->sn[0] = sin(best_x[2]);
         }
         __syncthreads();
-        find_correspondences<T, C>(s, L, n, ctl->x[0][0], ctl->x[0][1], ctl->cs[0], ctl->sn[0], min_theta, C1, maxd2, R);
+        it.x0 = ctl->x[0][0];
+        it.x1 = ctl->x[0][1];
+        it.cs = ctl->cs[0];
+        it.sn = ctl->sn[0];
+        valid = find_correspondences<T>(l, wc, it, C, sens);
     }
     if (t == 0) ctl->hash_acc[0] = 0;
-#pragma unroll
+#pragma unroll 1
     for (int k = 0; k < C; k++) {
         const int i = k * T + t;
-        if (i >= n) continue;
-        const bool cv = v_ok && (R.valid >> k & 1u);
-        const short j1 = cv ? (short)(R.cj[k] & 0xffff) : (short)-1;
-        const short j2 = cv ? (short)(R.cj[k] >> 16) : (short)-1;
-        s.cj1[i] = j1;
-        s.cj2[i] = j2;
-        if (oj1) { oj1[i] = j1; oj2[i] = j2; }
+        if (i >= n) break;
+        const bool cv = v_ok && (valid >> k & 1u);
+        if (!cv) { cj1[i] = -1; cj2[i] = -1; }
+        if (oj1) { oj1[i] = cj1[i]; oj2[i] = cj2[i]; }
     }
     __syncthreads();
     {
-        unsigned hc = corr_hash_chunk(s, n, t, a.hash_chunk, a.hashmat);
+        unsigned hc = corr_hash_chunk(l, n, t, a.hash_chunk, a.hashmat);
         hc = __reduce_xor_sync(0xffffffffu, hc);
         if (lane == 0 && hc) atomicXor(&ctl->hash_acc[0], hc);
     }
     __syncthreads();
     if (t == 0) {
         zhsm_result r = {};
-        r.valid = valid;
-        r.status = valid ? ZHSM_JOB_OK : status;
+        r.valid = valid_out;
+        r.status = valid_out ? ZHSM_JOB_OK : status;
         r.iterations = iterations;
         r.n_loops = n_loops;
-        if (valid) {
+        if (valid_out) {
             r.x[0] = best_x[0];
             r.x[1] = best_x[1];
             r.x[2] = best_x[2];

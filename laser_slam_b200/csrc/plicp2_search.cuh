@@ -4,7 +4,7 @@
 // last_best+1, the j1 of the previous ray that got a valid correspondence, and its jump tables may skip a closer
 // point, so the result depends on where the walk starts (the restatement differs from an exhaustive search on ~1 %
 // of real scan pairs).  The kernel reproduces it exactly: every ray is searched with a SPECULATED last_best
-// (the value the previous iteration saw), then verified against its actual predecessor and re-searched until
+// (the value the previous iteration saw, kept per ray in shared memory), then verified against its actual predecessor and re-searched until
 // nothing changes -- the fixpoint is the sequential result (induction over i).
 //
 // The walk itself is restated without libm calls.  CSM stops a direction when
@@ -44,11 +44,21 @@ __device__ __forceinline__ Ray make_ray(double2 p, double x0, double x1, double 
     return r;
 }
 
-// One ray's walk.  Returns j1 (a fully valid correspondence) or -1; fills d2 (dist2_j1) and j2.
-static __device__ __noinline__ int tricks_one(const Smem &s, const LaserDev &L, int n, const Ray &r, int last_best,
-                                       double maxd2, double *d2out, int *j2out) {
+// Geometry a walk needs besides the ray: offsets of the ref tables in shared memory and the beam angles.
+struct WalkCtx {
+    unsigned refp, rr2, jt;  // shared-memory byte offsets
+    int n;
+    float fi_min, dfi;
+    double maxd2;
+};
+
+// One ray's walk.  Returns j1 (a fully valid correspondence) or -1 and j2 in *j2out.
+static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int last_best, int *j2out) {
     const float HALF_PI_F = 1.57079632679489662f;
-    const int to = n - 1;
+    const int n = c.n, to = n - 1;
+    const double2 *refp = PL_SH(const double2, c.refp);
+    const double *rr2a = PL_SH(const double, c.rr2);
+    const short *jt = PL_SH(const short, c.jt);
     const double wx = r.wx, wy = r.wy, rho2 = r.rho2;
     const int start_cell = r.start_cell;
     int j1 = -1;
@@ -59,24 +69,23 @@ static __device__ __noinline__ int tricks_one(const Smem &s, const LaserDev &L, 
     int up = we_start_at + 1, down = we_start_at;
     double last_up = 0, last_down = -1;
     bool up_stopped = false, down_stopped = false;
-    const short *jt = s.jt;
     while (!(up_stopped && down_stopped)) {
         const bool now_up = up_stopped ? false : down_stopped ? true : (last_up < last_down);
-        int idx = now_up ? up : down;
+        const int idx = now_up ? up : down;
         if (now_up ? (idx > to) : (idx < 0)) {
             if (now_up) up_stopped = true; else down_stopped = true;
             continue;
         }
-        const double rr2 = s.rr2[idx];
+        const double rr2 = rr2a[idx];
         int step = now_up ? 1 : -1;
         bool stop = false;
         if (rr2 >= 0) {
-            const double2 q = s.refp[idx];
+            const double2 q = refp[idx];
             const double d = dist2(wx, wy, q.x, q.y);
             if (now_up) last_up = d; else last_down = d;
             if (d < best || j1 == -1) { j1 = idx; best = d; }
             if (now_up ? (idx > start_cell) : (idx < start_cell)) {
-                const float th = theta_f(L, idx);
+                const float th = theta_f(c.fi_min, c.dfi, idx);
                 const float dth = now_up ? th - r.phi : r.phi - th;
                 const double cross = wx * q.y - wy * q.x;
                 const bool far = dth > HALF_PI_F;
@@ -92,20 +101,19 @@ static __device__ __noinline__ int tricks_one(const Smem &s, const LaserDev &L, 
             if (now_up) up = idx + step; else down = idx + step;
         }
     }
-    if (j1 == -1 || best > maxd2) return -1;
+    if (j1 == -1 || best > c.maxd2) return -1;
     if (j1 == 0 || j1 == n - 1) return -1;
     int j2up = -1, j2down = -1;
-    for (int j = j1 + 1; j < n; j++) if (s.rr2[j] >= 0) { j2up = j; break; }
-    for (int j = j1 - 1; j >= 0; j--) if (s.rr2[j] >= 0) { j2down = j; break; }
+    for (int j = j1 + 1; j < n; j++) if (rr2a[j] >= 0) { j2up = j; break; }
+    for (int j = j1 - 1; j >= 0; j--) if (rr2a[j] >= 0) { j2down = j; break; }
     if (j2up == -1 && j2down == -1) return -1;
     int j2;
     if (j2up == -1) j2 = j2down;
     else if (j2down == -1) j2 = j2up;
     else {
-        const double2 qu = s.refp[j2up], qd = s.refp[j2down];
+        const double2 qu = refp[j2up], qd = refp[j2down];
         j2 = dist2(wx, wy, qu.x, qu.y) < dist2(wx, wy, qd.x, qd.y) ? j2up : j2down;
     }
-    *d2out = best;
     *j2out = j2;
     return j1;
 }
@@ -114,8 +122,9 @@ static __device__ __noinline__ int tricks_one(const Smem &s, const LaserDev &L, 
 // right-to-left (up tables) / left-to-right (down tables) and hopping over already-known runs:
 //   up_bigger[i] = first j>i that is invalid or has r[j] > r[i]; every entry up_bigger[m], final or still at its
 //   initial value 1, only skips points <= r[m], so hopping by it never skips the answer.  Exact, O(n) per table.
-__device__ inline void build_jump_tables(const Smem &s, int n, int t, int nthreads) {
-    volatile short *jt = s.jt;
+__device__ inline void build_jump_tables(const Lay &l, int n, int t, int nthreads) {
+    volatile short *jt = PL_SH(volatile short, l.jt);
+    const double *rr2a = PL_SH(const double, l.rr2);
     for (int i = t; i < n; i += nthreads) {
         jt[0 * n + i] = 1; jt[1 * n + i] = 1; jt[2 * n + i] = -1; jt[3 * n + i] = -1;
     }
@@ -123,21 +132,21 @@ __device__ inline void build_jump_tables(const Smem &s, int n, int t, int nthrea
     const int per = (n + nthreads - 1) / nthreads;
     const int lo = t * per, hi = (lo + per < n ? lo + per : n);
     for (int i = hi - 1; i >= lo; i--) {
-        const double ri = s.rr2[i];  // squares are monotone in r >= 0; invalid = -1 like the reading
+        const double ri = rr2a[i];  // squares are monotone in r >= 0; invalid = -1 like the reading
         int j = i + 1;
-        while (j < n) { double rj = s.rr2[j]; if (!(rj >= 0 && rj <= ri)) break; j += jt[0 * n + j]; }
+        while (j < n) { double rj = rr2a[j]; if (!(rj >= 0 && rj <= ri)) break; j += jt[0 * n + j]; }
         jt[0 * n + i] = (short)(j - i);
         j = i + 1;
-        while (j < n) { double rj = s.rr2[j]; if (!(rj >= 0 && rj >= ri)) break; j += jt[1 * n + j]; }
+        while (j < n) { double rj = rr2a[j]; if (!(rj >= 0 && rj >= ri)) break; j += jt[1 * n + j]; }
         jt[1 * n + i] = (short)(j - i);
     }
     for (int i = lo; i < hi; i++) {
-        const double ri = s.rr2[i];
+        const double ri = rr2a[i];
         int j = i - 1;
-        while (j >= 0) { double rj = s.rr2[j]; if (!(rj >= 0 && rj <= ri)) break; j += jt[2 * n + j]; }
+        while (j >= 0) { double rj = rr2a[j]; if (!(rj >= 0 && rj <= ri)) break; j += jt[2 * n + j]; }
         jt[2 * n + i] = (short)(j - i);
         j = i - 1;
-        while (j >= 0) { double rj = s.rr2[j]; if (!(rj >= 0 && rj >= ri)) break; j += jt[3 * n + j]; }
+        while (j >= 0) { double rj = rr2a[j]; if (!(rj >= 0 && rj >= ri)) break; j += jt[3 * n + j]; }
         jt[3 * n + i] = (short)(j - i);
     }
 }

@@ -24,11 +24,13 @@ __device__ __forceinline__ int block_sum(int v, int *ired, int slot) {
 // warp redundantly locates the buckets (no second barrier).  A bucket holding a single key ends that rank early
 // (the key's owner index is remembered next to the histogram); three rotating histogram sets make the zeroing of
 // the next set race-free.
-template <int T, int C>
-__device__ __forceinline__ void select2(const Smem &s, int n, unsigned valid, int rank0, int rank1, double &v0,
+template <int T>
+__device__ __forceinline__ void select2(const Lay &l, int C, unsigned valid, int rank0, int rank1, double &v0,
                                         double &v1) {
     const int t = threadIdx.x, lane = t & 31;
-    const unsigned long long *keyS = s.d2j;
+    const unsigned long long *keyS = PL_SH(const unsigned long long, l.d2j);
+    int *hist_all = PL_SH(int, l.hist);
+    short *cand_all = PL_SH(short, l.candi);
     unsigned long long prefix[2] = {0, 0};
     int rem[2] = {rank0, rank1};
     bool done[2] = {false, false};
@@ -37,11 +39,11 @@ __device__ __forceinline__ void select2(const Smem &s, int n, unsigned valid, in
 #pragma unroll 1
     for (int pass = 0; pass < 8; pass++) {
         const int shift = 56 - 8 * pass;
-        int *hist = s.hist + 256 * (pass % 3);
-        short *cand = s.candi + 512 * (pass % 3);
-        int *hnext = s.hist + 256 * ((pass + 1) % 3);
+        int *hist = hist_all + 256 * (pass % 3);
+        short *cand = cand_all + 512 * (pass % 3);
+        int *hnext = hist_all + 256 * ((pass + 1) % 3);
         for (int b = t; b < 256; b += T) hnext[b] = 0;
-#pragma unroll
+#pragma unroll 1
         for (int k = 0; k < C; k++) {
             if (!(valid >> k & 1u)) continue;
             const int i = k * T + t;
@@ -107,14 +109,15 @@ __device__ __forceinline__ void select2(const Smem &s, int n, unsigned valid, in
 // Both steps are affine over GF(2), so the hash of the whole stream is the XOR over chunks of
 // (linear map of the steps that follow the chunk) applied to (the chunk hashed from 0).  Thread t hashes the chunk
 // [t*ch, (t+1)*ch) (ch even) and multiplies by its 32x32 bit matrix hashmat[t] (built on the host by zhsm_set_laser).
-__device__ __forceinline__ unsigned corr_hash_chunk(const Smem &s, int n, int t, int ch, const uint32_t *hashmat) {
+__device__ __forceinline__ unsigned corr_hash_chunk(const Lay &l, int n, int t, int ch, const uint32_t *hashmat) {
+    const short *cj1 = PL_SH(const short, l.cj1), *cj2 = PL_SH(const short, l.cj2);
     const int lo = t * ch;
     if (lo >= n) return 0u;
     const int hi = lo + ch < n ? lo + ch : n;
     unsigned h = 0;
     for (int i = lo; i < hi; i++) {
-        const int j1 = s.cj1[i];
-        const unsigned v = j1 < 0 ? 0xffffffffu : (unsigned)(j1 + 1000 * (int)s.cj2[i]);
+        const int j1 = cj1[i];
+        const unsigned v = j1 < 0 ? 0xffffffffu : (unsigned)(j1 + 1000 * (int)cj2[i]);
         h ^= ((i & 1) == 0) ? ((h << 7) ^ v ^ (h >> 3)) : (~((h << 11) ^ v ^ (h >> 5)));
     }
     const uint4 *m = reinterpret_cast<const uint4 *>(hashmat + 32 * t);

@@ -145,7 +145,7 @@ extern "C" zhsm_status zhsm_set_laser(zhsm_handle *h, const zhsm_laser *laser) {
     {
         int T, C, ch;
         plicp_shape(n, &T, &C, &ch);
-        if (C < 0) { h->err = "no PL-ICP kernel instance for this beam count"; return ZHSM_ERR_UNSUPPORTED; }
+        if (C > 32) { h->err = "no PL-ICP kernel instance for this beam count"; return ZHSM_ERR_UNSUPPORTED; }
         std::vector<uint32_t> mat;
         plicp_build_hash_matrices(n, T, ch, mat);
         if (h->d_hashmat) { cudaFree(h->d_hashmat); h->d_hashmat = nullptr; }
@@ -164,7 +164,7 @@ extern "C" int zhsm_debug_corr_hash(const int32_t *stream, int n, uint32_t *seq,
     if (!stream || n < 1 || n > ZHSM_MAX_BEAMS || !seq || !par) return 1;
     int T, C, ch;
     plicp_shape(n, &T, &C, &ch);
-    if (C < 0) return 2;
+    if (C > 32) return 2;
     std::vector<uint32_t> mat;
     plicp_build_hash_matrices(n, T, ch, mat);
     uint32_t h = 0;

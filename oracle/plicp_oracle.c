@@ -243,14 +243,28 @@ static void finish_corr(const orc_sm_params *params, orc_laser_data *ref, orc_la
 
 /* find_correspondences_tricks [UPSTREAM sm/csm/icp/icp_corr_tricks.c]: SURVEY 8a-4.
  * Selected by use_corr_tricks=1 (ZHCanonical_Matcher.cpp:106). */
+/* analysis counters (single-thread runs only): distance evaluations, rays searched, and the sum over groups of 32
+ * consecutive rays of the slowest ray's evaluations -- the cost model of a 32-lane lock-step walk */
+static long long g_walk_visits, g_walk_rays, g_walk_warpmax, g_walk_calls;
+void orc_debug_walk_stats(long long out[4], int reset) {
+    out[0] = g_walk_visits; out[1] = g_walk_rays; out[2] = g_walk_warpmax; out[3] = g_walk_calls;
+    if (reset) g_walk_visits = g_walk_rays = g_walk_warpmax = g_walk_calls = 0;
+}
+
 static void find_correspondences_tricks(orc_sm_params *params) {
+    long long visits_this = 0, group_max = 0;
+    g_walk_calls++;
     orc_laser_data *laser_ref = params->laser_ref;
     orc_laser_data *laser_sens = params->laser_sens;
     double C1 = (double)laser_ref->nrays / (laser_ref->max_theta - laser_ref->min_theta);
     double max_correspondence_dist2 = SQ(params->max_correspondence_dist);
     int last_best = -1;
     for (int i = 0; i < laser_sens->nrays; i++) {
+        if ((i & 31) == 0) { g_walk_warpmax += group_max; group_max = 0; }
+        if (visits_this > group_max) group_max = visits_this;
+        visits_this = 0;
         if (!ld_valid_ray(laser_sens, i)) { ld_set_null_corr(laser_sens, i); continue; }
+        g_walk_rays++;
         double pwx = laser_sens->wx[i], pwy = laser_sens->wy[i];
         double p_i_w_nrm2 = laser_sens->wrho[i];
         double p_i_w_phi = laser_sens->wphi[i];
@@ -273,6 +287,7 @@ static void find_correspondences_tricks(orc_sm_params *params) {
                 if (up > to) { up_stopped = 1; continue; }
                 if (!laser_ref->valid[up]) { ++up; continue; }
                 last_dist_up = dist2_d(pwx, pwy, laser_ref->px[up], laser_ref->py[up]);
+                g_walk_visits++; visits_this++;
                 if (last_dist_up < best_dist || j1 == -1) { j1 = up; best_dist = last_dist_up; }
                 if (up > start_cell) {
                     double delta_theta = laser_ref->theta[up] - p_i_w_phi;
@@ -288,6 +303,7 @@ static void find_correspondences_tricks(orc_sm_params *params) {
                 if (down < from) { down_stopped = 1; continue; }
                 if (!laser_ref->valid[down]) { --down; continue; }
                 last_dist_down = dist2_d(pwx, pwy, laser_ref->px[down], laser_ref->py[down]);
+                g_walk_visits++; visits_this++;
                 if (last_dist_down < best_dist || j1 == -1) { j1 = down; best_dist = last_dist_down; }
                 if (down < start_cell) {
                     double delta_theta = p_i_w_phi - laser_ref->theta[down];
