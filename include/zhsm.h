@@ -151,6 +151,9 @@ double zhsm_fp_peak_tflops(zhsm_handle *h, int which);
 /* test hook, host only: ld_corr_hash of a correspondence stream (j1 + 1000*j2, or -1) evaluated sequentially
  * (seq) and with the kernel's chunk/GF(2)-matrix decomposition (par).  Returns 0 on success. */
 int zhsm_debug_corr_hash(const int32_t *stream, int n, uint32_t *seq, uint32_t *par);
+/* test hook, device: greatest real root of B quartics a0 + a1 x + .. + a4 x^4 (host arrays coef[B][5], root[B],
+ * ok[B]) by the warp-cooperative solver the PL-ICP kernel uses for gpc_solve's lambda. */
+zhsm_status zhsm_debug_quartic_roots(zhsm_handle *h, const double *coef, int B, double *root, int *ok);
 
 #ifdef __cplusplus
 }

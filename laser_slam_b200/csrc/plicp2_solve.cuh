@@ -17,42 +17,52 @@ __device__ __forceinline__ double poly_eval(const double *c, int deg, double x) 
 }
 
 // Root of f = c[0..DEG] on [lo,hi], where f is monotone and f(lo), f(hi) have opposite signs (or one is 0).
-// Warp-wide 33-section (each lane probes one point, the ballot locates the sign change), then Newton polish.
+// Warp-wide 33-section (each lane probes one point, the ballot locates the sign change): 4 rounds shrink the bracket
+// 1.2e6 times, then Newton (quadratic) reaches rounding in 2-3 steps; if Newton leaves the bracket or stalls
+// (ill-conditioned root) four more section rounds finish the job.
 template <int DEG>
-__device__ __forceinline__ double root_monotone_warp(const double *c, double lo, double hi, double flo) {
+__device__ __forceinline__ void section_rounds(const double *c, double &lo, double &hi, bool lo_neg, int rounds) {
     const int lane = threadIdx.x & 31;
-    const bool lo_neg = flo < 0;
 #pragma unroll 1
-    for (int round = 0; round < 7; round++) {
-        double w = (hi - lo) * (1.0 / 33.0);
-        double x = lo + w * (double)(lane + 1);
-        double fx = poly_eval(c, DEG, x);
-        bool same = (fx != 0) && ((fx < 0) == lo_neg);
-        unsigned m = __ballot_sync(0xffffffffu, same);
-        int cnt = __ffs(~m) - 1;  // length of the same-sign prefix (32 when all lanes agree with lo)
-        if (m == 0xffffffffu) cnt = 32;
-        double nlo = cnt == 0 ? lo : lo + w * (double)cnt;
-        double nhi = cnt == 32 ? hi : lo + w * (double)(cnt + 1);
+    for (int round = 0; round < rounds; round++) {
+        const double w = (hi - lo) * (1.0 / 33.0);
+        const double x = lo + w * (double)(lane + 1);
+        const double fx = poly_eval(c, DEG, x);
+        const bool same = (fx != 0) && ((fx < 0) == lo_neg);
+        const unsigned m = __ballot_sync(0xffffffffu, same);
+        const int cnt = (m == 0xffffffffu) ? 32 : (__ffs(~m) - 1);  // length of the same-sign prefix
+        const double nlo = cnt == 0 ? lo : lo + w * (double)cnt;
+        const double nhi = cnt == 32 ? hi : lo + w * (double)(cnt + 1);
         if (!(nhi > nlo)) break;
         lo = nlo;
         hi = nhi;
     }
-    // Newton from the midpoint, clamped to the bracket (33^7 ~ 4e10 shrink already; two steps reach rounding)
+}
+
+template <int DEG>
+__device__ __forceinline__ double root_monotone_warp(const double *c, double lo, double hi, double flo) {
+    const bool lo_neg = flo < 0;
+    section_rounds<DEG>(c, lo, hi, lo_neg, 4);
     double dc[DEG];
 #pragma unroll
     for (int i = 1; i <= DEG; i++) dc[i - 1] = c[i] * i;
     double x = 0.5 * (lo + hi);
+    bool converged = false;
 #pragma unroll 1
-    for (int it = 0; it < 4; it++) {
-        double fx = poly_eval(c, DEG, x);
-        double dfx = poly_eval(dc, DEG - 1, x);
-        if (fx == 0 || dfx == 0) break;
-        double xn = x - fx / dfx;
+    for (int it = 0; it < 5; it++) {
+        const double fx = poly_eval(c, DEG, x);
+        if (fx == 0) { converged = true; break; }
+        const double dfx = poly_eval(dc, DEG - 1, x);
+        if (dfx == 0) break;
+        const double xn = x - fx / dfx;
         if (!(xn >= lo && xn <= hi)) break;
-        if (xn == x) break;
+        const double step = fabs(xn - x);
         x = xn;
+        if (step <= 4e-16 * fabs(x)) { converged = true; break; }
     }
-    return x;
+    if (converged) return x;
+    section_rounds<DEG>(c, lo, hi, lo_neg, 6);
+    return 0.5 * (lo + hi);
 }
 
 // upper bound on |root| for c[0..deg] (Fujiwara): 2*max_k |c[deg-k]/c[deg]|^(1/k)
@@ -67,28 +77,34 @@ __device__ __forceinline__ double root_bound(const double *c, int deg) {
     return 2.0 * b * (1.0 + 1e-9) + 1e-300;
 }
 
-// All real roots (ascending) of c[0..DEG] given the real roots of its derivative; warp-cooperative.
-template <int DEG>
-__device__ __forceinline__ int roots_from_crit_warp(const double *c, const double *crit, int nc, double *roots) {
-    double B = root_bound(c, DEG);
-    double pts[DEG + 1];
-    int np = 0;
-    pts[np++] = -B;
-    for (int i = 0; i < nc; i++) if (crit[i] > -B && crit[i] < B) pts[np++] = crit[i];
-    pts[np++] = B;
-    int nr = 0;
-    for (int i = 0; i + 1 < np; i++) {
-        double a = pts[i], b = pts[i + 1];
-        double fa = poly_eval(c, DEG, a), fb = poly_eval(c, DEG, b);
-        if (fa == 0) { if (nr == 0 || roots[nr - 1] != a) roots[nr++] = a; continue; }
-        if ((fa < 0) != (fb < 0) && fb != 0) roots[nr++] = root_monotone_warp<DEG>(c, a, b, fa);
-        else if (fb == 0 && i + 2 == np) roots[nr++] = b;
+// Real roots of the cubic c[0..3], produced lazily in DESCENDING order from its monotone pieces (split at the
+// roots r2[0..n2) of its derivative).  *piece walks from the right-most piece down; returns false when exhausted.
+__device__ __forceinline__ bool next_cubic_root_desc(const double *c, const double *pts, int np, int *piece,
+                                                     double *last, bool *have_last, double *root) {
+    while (*piece >= 0) {
+        const int i = *piece;
+        (*piece)--;
+        const double a = pts[i], b = pts[i + 1];
+        const double fa = poly_eval(c, 3, a), fb = poly_eval(c, 3, b);
+        if (fb == 0) {
+            if (!*have_last || *last != b) { *last = b; *have_last = true; *root = b; (*piece)++; 
+                // revisit the same piece for a possible interior root / fa == 0 after reporting b
+                // (handled by the branch below on the next call through the have_last guard)
+                return true; }
+        }
+        if (fa != 0 && fb != 0 && ((fa < 0) != (fb < 0))) {
+            const double r = root_monotone_warp<3>(c, a, b, fa);
+            *last = r; *have_last = true; *root = r;
+            return true;
+        }
+        if (fa == 0 && i == 0 && (!*have_last || *last != a)) { *last = a; *have_last = true; *root = a; return true; }
     }
-    return nr;
+    return false;
 }
 
-// greatest real root of the quartic a[0..4] (poly_greatest_real_root of gpc.c).  Fast path: the right-most
-// monotone piece [greatest critical point, bound]; general path: the full derivative chain.
+// greatest real root of the quartic a[0..4] (poly_greatest_real_root of gpc.c): walk the monotone pieces of the
+// quartic from the right (the pieces are bounded by the real roots of its derivative, taken in descending order)
+// and solve in the first piece whose ends differ in sign.  Typical cost: one cubic root + one quartic root.
 static __device__ __noinline__ bool greatest_real_root4_warp(const double *a, double *root) {
     if (a[4] == 0 || isnan(a[4])) return false;
     double d3[4], d2[3];
@@ -96,30 +112,49 @@ static __device__ __noinline__ bool greatest_real_root4_warp(const double *a, do
     for (int i = 1; i <= 4; i++) d3[i - 1] = a[i] * i;
 #pragma unroll
     for (int i = 1; i <= 3; i++) d2[i - 1] = d3[i] * i;
-    // roots of the quadratic d2 (closed form, ascending)
-    double r2[2];
-    int n2 = 0;
+    // monotone pieces of the cubic: [-B3, roots of the quadratic d2 (closed form, ascending), B3]
+    const double B3 = root_bound(d3, 3);
+    double pts[4];
+    int np = 0;
+    pts[np++] = -B3;
     {
-        double A = d2[2], Bq = d2[1], Cq = d2[0];
-        double disc = Bq * Bq - 4 * A * Cq;
+        const double A = d2[2], Bq = d2[1], Cq = d2[0];
+        const double disc = Bq * Bq - 4 * A * Cq;
         if (disc > 0) {
-            double sq = sqrt(disc);
-            double qq = -0.5 * (Bq + (Bq >= 0 ? sq : -sq));
-            double x1 = qq / A, x2 = (qq != 0) ? Cq / qq : x1;
-            r2[0] = x1 < x2 ? x1 : x2;
-            r2[1] = x1 < x2 ? x2 : x1;
-            n2 = 2;
+            const double sq = sqrt(disc);
+            const double qq = -0.5 * (Bq + (Bq >= 0 ? sq : -sq));
+            const double x1 = qq / A, x2 = (qq != 0) ? Cq / qq : x1;
+            const double lo = x1 < x2 ? x1 : x2, hi = x1 < x2 ? x2 : x1;
+            if (lo > -B3 && lo < B3) pts[np++] = lo;
+            if (hi > -B3 && hi < B3 && hi != lo) pts[np++] = hi;
         } else if (disc == 0) {
-            r2[0] = -Bq / (2 * A);
-            n2 = 1;
+            const double x = -Bq / (2 * A);
+            if (x > -B3 && x < B3) pts[np++] = x;
         }
     }
-    double r3[3], r4[4];
-    int n3 = roots_from_crit_warp<3>(d3, r2, n2, r3);
-    int n4 = roots_from_crit_warp<4>(a, r3, n3, r4);
-    if (n4 == 0) return false;
-    *root = r4[n4 - 1];
-    return true;
+    pts[np++] = B3;
+    int piece = np - 2;
+    double last = 0;
+    bool have_last = false;
+    const double B4 = root_bound(a, 4);
+    double hi = B4, fhi = poly_eval(a, 4, hi);
+    if (fhi == 0) { *root = hi; return true; }
+    if (isnan(fhi)) return false;
+#pragma unroll 1
+    for (int guard = 0; guard < 8; guard++) {
+        double c;
+        const bool more = next_cubic_root_desc(d3, pts, np, &piece, &last, &have_last, &c);
+        double lo = more ? c : -B4;
+        if (lo >= hi) { if (!more) return false; continue; }
+        if (lo < -B4) lo = -B4;
+        const double flo = poly_eval(a, 4, lo);
+        if (flo == 0) { *root = lo; return true; }
+        if ((flo < 0) != (fhi < 0)) { *root = root_monotone_warp<4>(a, lo, hi, flo); return true; }
+        if (!more || lo <= -B4) return false;
+        hi = lo;
+        fhi = flo;
+    }
+    return false;
 }
 
 __device__ __forceinline__ bool inv2(const double A[2][2], double inv[2][2]) {

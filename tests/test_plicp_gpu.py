@@ -42,3 +42,47 @@ def test_plicp_matches_oracle_goldens(engine, log):
     assert hash_eq.mean() >= 0.999
     # correspondence arrays are self-consistent with the hash stream semantics
     assert ((j1 >= -1) & (j1 < int(g["n"]))).all() and ((j1 < 0) == (j2 < 0)).all()
+
+
+def test_quartic_greatest_root_solver(engine):
+    """gpc_solve's lambda: the warp-cooperative solver vs numpy's companion-matrix roots (what GSL does)."""
+    import ctypes as C
+    rng = np.random.default_rng(11)
+    polys, want = [], []
+    for k in range(4000):
+        kind = k % 4
+        if kind == 0:      # four real roots
+            r = rng.uniform(-50, 50, 4)
+            p = np.poly(r); w = r.max()
+        elif kind == 1:    # two real + a complex pair (possibly to the right of the real roots)
+            r = rng.uniform(-30, 30, 2); re, im = rng.uniform(-40, 40), rng.uniform(0.05, 20)
+            p = np.polymul(np.poly(r), [1, -2 * re, re * re + im * im]); w = r.max()
+        elif kind == 2:    # GPC-like: q = p2(x) - l(x)^2, negative leading coefficient, widely spread scales
+            l = np.array([4.0, rng.uniform(1, 1e4), rng.uniform(1, 1e6)])
+            p2 = np.array([rng.uniform(0, 1e6), rng.uniform(-1e8, 1e8), rng.uniform(0, 1e12)])
+            p = -np.polymul(l, l); p[2:] += p2
+            rr = np.roots(p); rr = rr[np.abs(rr.imag) < 1e-9 * (1 + np.abs(rr.real))].real
+            if rr.size == 0:
+                continue
+            w = rr.max()
+        else:              # no real root
+            re1, im1, re2, im2 = rng.uniform(-5, 5), rng.uniform(0.5, 5), rng.uniform(-5, 5), rng.uniform(0.5, 5)
+            p = np.polymul([1, -2 * re1, re1 ** 2 + im1 ** 2], [1, -2 * re2, re2 ** 2 + im2 ** 2]); w = None
+        p = p * rng.choice([-1, 1]) * rng.uniform(0.1, 100)
+        polys.append(p[::-1].copy()); want.append(w)
+    coef = np.ascontiguousarray(np.array(polys), np.float64)
+    B = coef.shape[0]
+    root = np.zeros(B); ok = np.zeros(B, np.int32)
+    engine.L.zhsm_debug_quartic_roots.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+    st = engine.L.zhsm_debug_quartic_roots(engine.h, coef.ctypes.data, B, root.ctypes.data, ok.ctypes.data)
+    assert st == 0
+    bad = 0
+    for k in range(B):
+        if want[k] is None:
+            assert ok[k] == 0, (k, coef[k], root[k])
+        else:
+            assert ok[k] == 1, (k, coef[k])
+            if abs(root[k] - want[k]) > 1e-6 * max(1.0, abs(want[k])):
+                bad += 1
+    # ill-conditioned (nearly double) greatest roots may differ in the low digits; anything else is a bug
+    assert bad <= B // 500, bad
