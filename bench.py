@@ -28,6 +28,8 @@ N_BEAMS = 1080
 FOV_DEG = 270.0
 MAX_RANGE_CM = 3000
 SEED = 20261104
+# dram__bytes_read.sum + dram__bytes_write.sum of plicp2_kernel per pair (profiles/r01c_*: 175.5 MB + 30.1 MB / 20000 pairs)
+NCU_DRAM_BYTES_PER_PAIR = (175.535360e6 + 30.145280e6) / 20000
 
 
 def make_laser(zh):
@@ -177,6 +179,7 @@ def run_ours(args):
     import torch
     import torch.distributed as dist
     import laser_slam_b200 as zh
+    from laser_slam_b200 import shard
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -204,7 +207,7 @@ def run_ours(args):
     ri = torch.arange(0, 2 * P, 2, dtype=torch.int32, device=dev)
     si = ri + 1
     res = torch.zeros((P, 128), dtype=torch.uint8, device=dev)
-    gathered = torch.empty((world * P, 128), dtype=torch.uint8, device=dev) if world > 1 else None
+    gathered = [None]
     torch.cuda.synchronize()
 
     def barrier():
@@ -226,7 +229,7 @@ def run_ours(args):
             e1.record()
             kern_events.append((e0, e1))
         if world > 1:
-            dist.all_gather_into_tensor(gathered, res)
+            gathered[0] = shard.all_gather_records(res, world * P)
 
     for _ in range(args.warmup):
         step()
@@ -320,8 +323,11 @@ def run_ours(args):
                         "device_vs_host_path_identical": same},
                 "gpu_launches": int(launches),
                 "roofline": {"bound": "fp64_cuda_core", "achieved": achieved, "peak": peak64, "unit": "TFLOP/s",
-                             "frac": achieved / peak64 if peak64 > 0 else None, "traffic": None,
-                             "kernel": "plicp_kernel", "kernel_ms": kern_ms,
+                             "frac": achieved / peak64 if peak64 > 0 else None,
+                             "traffic": NCU_DRAM_BYTES_PER_PAIR * P,
+                             "traffic_source": "ncu --set full dram__bytes_read+write of a 20k-pair launch "
+                                               "(profiles/), scaled by pairs per launch",
+                             "kernel": "plicp2_kernel<256>", "kernel_ms": kern_ms,
                              "peak_source": "DFMA micro-benchmark measured in this run (zhsm_fp_peak_tflops)",
                              "fp32_peak": peak32, "frac_of_fp32_peak": achieved / peak32 if peak32 > 0 else None,
                              "algorithmic_flops_per_launch": flops, **fl_detail,

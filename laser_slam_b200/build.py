@@ -57,5 +57,31 @@ def build(force=False, verbose=False):
     return OUT
 
 
+def build_host(verbose=False):
+    """The C++ host shim (laser_slam_b200/host: CCanonicalMatcher with the reference's interface) as
+    libzhsm_host.so, plus the C++ test driver tests/cpp/_build/shim_runlog that the GPU tests execute."""
+    root = os.path.dirname(HERE)
+    host = os.path.join(HERE, "host")
+    out = os.path.join(HERE, "libzhsm_host.so")
+    srcs = [os.path.join(host, "ZHCanonical_Matcher.cpp")]
+    deps = srcs + [os.path.join(host, f) for f in os.listdir(host) if f.endswith(".h")] + [os.path.join(root, "include", "zhsm.h")]
+    cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+    if not os.path.exists(out) or os.path.getmtime(out) < newest(deps):
+        cmd = [cxx, "-O2", "-std=c++17", "-Wall", "-fPIC", "-shared", "-I" + os.path.join(root, "include"), "-o", out] + srcs + \
+              ["-L" + HERE, "-lzhsm", "-Wl,-rpath,$ORIGIN"]
+        subprocess.run(cmd, check=True)
+    tdir = os.path.join(root, "tests", "cpp")
+    bdir = os.path.join(tdir, "_build")
+    os.makedirs(bdir, exist_ok=True)
+    exe = os.path.join(bdir, "shim_runlog")
+    src = os.path.join(tdir, "shim_runlog.cpp")
+    if not os.path.exists(exe) or os.path.getmtime(exe) < newest(deps + [src, out]):
+        cmd = [cxx, "-O2", "-std=c++17", "-Wall", "-I" + os.path.join(root, "include"), "-I" + host, "-o", exe, src,
+               "-L" + HERE, "-lzhsm_host", "-lzhsm", "-Wl,-rpath," + HERE]
+        subprocess.run(cmd, check=True)
+    return out, exe
+
+
 if __name__ == "__main__":
     build(force="--force" in sys.argv, verbose=True)
+    build_host()
