@@ -3,6 +3,7 @@
 // the parameters of sm_init (:83-157).  SURVEY 8a-2..8a-8.  FP64 throughout (CSM is double end to end), -fmad=false.
 #pragma once
 #include "plicp2_common.cuh"
+#include "plicp2_cov.cuh"
 #include "plicp2_search.cuh"
 #include "plicp2_select.cuh"
 #include "plicp2_solve.cuh"
@@ -363,8 +364,7 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
     const int fin = ctl->fin;
     const bool v_ok = fin & 1, v_restarted = fin & 2;
     __syncthreads();
-    if (v_ok && v_restarted) {
-        // "recompute correspondences in case of restarts" (icp.c): world coords at best x + tricks, no outlier pass
+    if (v_ok) {
         if (t == 0) {
             for (int k = 0; k < 3; k++) ctl->x[0][k] = best_x[k];
             ctl->cs[0] = cos(best_x[2]);
@@ -375,7 +375,8 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
         it.x1 = ctl->x[0][1];
         it.cs = ctl->cs[0];
         it.sn = ctl->sn[0];
-        valid = find_correspondences<T>(l, wc, it, C, sens);
+        // "recompute correspondences in case of restarts" (icp.c): world coords at best x + tricks, no outlier pass
+        if (v_restarted) valid = find_correspondences<T>(l, wc, it, C, sens);
     }
     if (t == 0) ctl->hash_acc[0] = 0;
 #pragma unroll 1
@@ -393,6 +394,9 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
         if (lane == 0 && hc) atomicXor(&ctl->hash_acc[0], hc);
     }
     __syncthreads();
+    double cov[6] = {0, 0, 0, 0, 0, 0};
+    if (v_ok && P.do_compute_covariance)
+        covariance_exact<T>(l, n, C, a.cs, it.x0, it.x1, it.cs, it.sn, P.sigma, cov);
     if (t == 0) {
         zhsm_result r = {};
         r.valid = valid_out;
@@ -406,6 +410,7 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
             r.error = best_error;
             r.nvalid = nvalid0;
             r.corr_hash = ctl->hash_acc[0] & 0x7FFFFFFFu;
+            for (int q = 0; q < 6; q++) r.cov[q] = cov[q];
         }
         *res = r;
     }

@@ -260,7 +260,6 @@ extern "C" zhsm_status zhsm_plicp_batch(zhsm_handle *h, const float *scans, int 
         h->err = "only use_corr_tricks=1 / use_point_to_line_distance=1 (the reference's settings) are implemented";
         return ZHSM_ERR_UNSUPPORTED;
     }
-    if (P.do_compute_covariance) { h->err = "do_compute_covariance not implemented yet"; return ZHSM_ERR_UNSUPPORTED; }
     if (P.max_iterations < 1 || P.max_iterations > ZHSM_MAX_ITER) { h->err = "max_iterations out of [1,64]"; return ZHSM_ERR_ARG; }
     ZHSM_CUDA_TRY(h, cudaSetDevice(h->device));
     cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : h->stream;

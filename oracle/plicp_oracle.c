@@ -245,7 +245,7 @@ static void finish_corr(const orc_sm_params *params, orc_laser_data *ref, orc_la
  * Selected by use_corr_tricks=1 (ZHCanonical_Matcher.cpp:106). */
 /* analysis counters (single-thread runs only): distance evaluations, rays searched, and the sum over groups of 32
  * consecutive rays of the slowest ray's evaluations -- the cost model of a 32-lane lock-step walk */
-static long long g_walk_visits, g_walk_rays, g_walk_warpmax, g_walk_calls;
+static __thread long long g_walk_visits, g_walk_rays, g_walk_warpmax, g_walk_calls; /* thread-local: no sharing between the batch workers */
 void orc_debug_walk_stats(long long out[4], int reset) {
     out[0] = g_walk_visits; out[1] = g_walk_rays; out[2] = g_walk_warpmax; out[3] = g_walk_calls;
     if (reset) g_walk_visits = g_walk_rays = g_walk_warpmax = g_walk_calls = 0;

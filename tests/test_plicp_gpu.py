@@ -86,3 +86,34 @@ def test_quartic_greatest_root_solver(engine):
                 bad += 1
     # ill-conditioned (nearly double) greatest roots may differ in the low digits; anything else is a bug
     assert bad <= B // 500, bad
+
+
+@pytest.mark.parametrize("log", ["intel-lab", "fr079"])
+def test_plicp_covariance_matches_oracle(engine, log):
+    """compute_covariance_exact (setCov(true), ZHCanonical_Matcher.cpp:79-81,292-296): sigma^2 * cov0, relative 1e-6
+    (the kernel evaluates the reference's trigonometry algebraically)."""
+    from oracle import pyoracle as po
+    g = load_log(log)
+    engine.set_laser(make_laser(g))
+    S = 200
+    scans = engine.median_filter(g["scans"][:S].copy())
+    p = engine.default_plicp_params()
+    p.do_compute_covariance = 1
+    res = engine.plicp(scans, np.arange(S - 1), np.arange(1, S), params=p)
+    lz = make_laser(g)
+    o = po.zhcsm_fmatch_batch(scans, np.arange(S - 1), np.arange(1, S), lz.fi_min, lz.dfi, lz.min_range_cm,
+                              lz.max_range_cm, params=po.default_params(lz.min_range_cm, lz.max_range_cm,
+                                                                        do_compute_covariance=1), nthreads=8)
+    same = (res["valid"] == 1) & (o["valid"] == 1) & (res["corr_hash"] == o["corr_hash"])
+    assert same.mean() > 0.99
+    oc = o["cov"].reshape(-1, 3, 3)
+    want = np.stack([oc[:, 0, 0], oc[:, 0, 1], oc[:, 0, 2], oc[:, 1, 1], oc[:, 1, 2], oc[:, 2, 2]], 1)
+    got = res["cov"]
+    scale = np.abs(want).max(1, keepdims=True)
+    rel = np.abs(got - want) / scale
+    assert np.isfinite(got[same]).all()
+    assert rel[same].max() < 1e-6, rel[same].max()
+    # symmetric positive semi-definite, and without the flag the record carries zeros
+    assert (got[same][:, [0, 3, 5]] >= 0).all()
+    res0 = engine.plicp(scans, np.arange(S - 1), np.arange(1, S))
+    assert np.all(res0["cov"] == 0) and np.array_equal(res0["x"], res["x"])
