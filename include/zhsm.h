@@ -130,6 +130,38 @@ zhsm_status zhsm_plicp_batch(zhsm_handle *h, const float *scans, int S, const in
                              const zhsm_plicp_params *params, zhsm_result *results, int16_t *corr_j1,
                              int16_t *corr_j2, unsigned flags, void *cuda_stream);
 
+/* ---- zhpsm: polar scan matching and pm_icp (src/zhpsm/ZHPolar_Match.cpp) ---------------------------------------
+ * Scans are preprocessed once (zhsm_preprocess_batch) and then matched any number of times.  bad holds the
+ * reference's PM_RANGE / PM_OCCLUDED / PM_EMPTY bit flags (PolarParameter.h:5-9) as uint8, seg the segment numbers of
+ * pm_segment_scan as int16.  Poses are PMScan units: cm, cm, rad.  The ref scan of a job sits at the origin, which is
+ * how every caller uses the matchers (CPolarMatch::FMatch zeroes both poses, ZHPolar_Match.cpp:97-99). */
+enum {
+    ZHSM_ALGO_PSM = 0,     /* CPolarMatch::pm_psm (:890-1003) */
+    ZHSM_ALGO_PM_ICP = 1,  /* CPolarMatch::pm_icp (:1653-2021) */
+    ZHSM_ALGO_PSM_ICP = 2, /* pm_psm, then pm_icp seeded with its result (runlog :561-563) */
+    ZHSM_ALGO_FMATCH = 3   /* CPolarMatch::FMatch (:81-121) on preprocessed scans: zero poses, pm_icp, pm_error_index2 */
+};
+
+/* pm_preprocessScan (:861-866) over S scans: pm_median_filter in place, pm_find_far_points (bad |= PM_RANGE),
+ * pm_segment_scan.  bad is in/out (pass zeros for fresh scans).  ZHSM_SCANS_ON_DEVICE covers all three arrays. */
+zhsm_status zhsm_preprocess_batch(zhsm_handle *h, float *scans, uint8_t *bad, int16_t *seg, int S, unsigned flags,
+                                  void *cuda_stream);
+
+/* Batched matcher.  init_pose: [B][3] float act poses or NULL (zeros).  Per job: results[k].x = pose (cm, cm, rad),
+ * .error = the matcher's return value, .iterations, .valid / .status (the reference's `throw 1` becomes
+ * ZHSM_JOB_TOO_FEW_POINTS / SINGULAR / SEARCH_FAILED and leaves the pose at init_pose, like the reference leaves
+ * lsa untouched).  ZHSM_ALGO_FMATCH also fills .cov[0], .cov[3] with the pair FMatch returns (avg_err_x, avg_err_y in
+ * m^2; -1,-1 on failure) and .nvalid with pm_error_index2's associated points.
+ * flags: ZHSM_SCANS_ON_DEVICE (scans, bad, seg), ZHSM_JOBS_ON_DEVICE (ref_idx, act_idx, init_pose),
+ * ZHSM_RESULTS_ON_DEVICE. */
+zhsm_status zhsm_psm_batch(zhsm_handle *h, const float *scans, const uint8_t *bad, const int16_t *seg, int S,
+                           const int32_t *ref_idx, const int32_t *act_idx, const float *init_pose, int B, int algo,
+                           zhsm_result *results, unsigned flags, void *cuda_stream);
+
+/* pm_scan_project (:1356-1479) of scan idx[k] at pose[k]: new_r [B][n] float, new_bad [B][n] uint8.  Host buffers. */
+zhsm_status zhsm_scan_project_batch(zhsm_handle *h, const float *scans, const uint8_t *bad, const int16_t *seg, int S,
+                                    const int32_t *idx, const float *pose, int B, float *new_r, uint8_t *new_bad);
+
 /* blocks until everything queued on the handle's stream (or the given one) is done */
 zhsm_status zhsm_sync(zhsm_handle *h, void *cuda_stream);
 
@@ -153,6 +185,9 @@ double zhsm_fp_peak_tflops(zhsm_handle *h, int which);
 int zhsm_debug_corr_hash(const int32_t *stream, int n, uint32_t *seq, uint32_t *par);
 /* test hook, device: greatest real root of B quartics a0 + a1 x + .. + a4 x^4 (host arrays coef[B][5], root[B],
  * ok[B]) by the warp-cooperative solver the PL-ICP kernel uses for gpc_solve's lambda. */
+/* test hook, device: out[k] = f(x[k], y[k]) with f = 0 sinf, 1 cosf, 2 atan2f(x = y-arg, y = x-arg) evaluated by the
+ * device routines that mirror the host libm bit for bit (csrc/zh_libm.cuh).  Host arrays. */
+zhsm_status zhsm_debug_libm(zhsm_handle *h, int which, const float *x, const float *y, float *out, int N);
 zhsm_status zhsm_debug_quartic_roots(zhsm_handle *h, const double *coef, int B, double *root, int *ok);
 
 #ifdef __cplusplus

@@ -53,7 +53,7 @@ cudaError_t median_filter_launch(float *scans, int S, int n, cudaStream_t st) {
 // ---------------------------------------------------------------------------------------------------------
 // handle
 // ---------------------------------------------------------------------------------------------------------
-static zhsm_status stage(zhsm_handle *h, int slot, size_t bytes, void **out) {
+zhsm_status zhsm_stage(zhsm_handle *h, int slot, size_t bytes, void **out) {
     if (h->stage_bytes[slot] < bytes) {
         if (h->d_stage[slot]) cudaFree(h->d_stage[slot]);
         h->d_stage[slot] = nullptr;
@@ -98,7 +98,10 @@ extern "C" void zhsm_destroy(zhsm_handle *h) {
     if (!h) return;
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
-    for (int i = 0; i < 8; i++) if (h->d_stage[i]) cudaFree(h->d_stage[i]);
+    for (int i = 0; i < 16; i++) if (h->d_stage[i]) cudaFree(h->d_stage[i]);
+    if (h->d_fi) cudaFree(h->d_fi);
+    if (h->d_si) cudaFree(h->d_si);
+    if (h->d_co) cudaFree(h->d_co);
     if (h->d_cs) cudaFree(h->d_cs);
     if (h->d_hashmat) cudaFree(h->d_hashmat);
     if (h->ev0) cudaEventDestroy(h->ev0);
@@ -141,6 +144,22 @@ extern "C" zhsm_status zhsm_set_laser(zhsm_handle *h, const zhsm_laser *laser) {
     if (h->d_cs) { cudaFree(h->d_cs); h->d_cs = nullptr; }
     ZHSM_CUDA_TRY(h, cudaMalloc(&h->d_cs, sizeof(double2) * n));
     ZHSM_CUDA_TRY(h, cudaMemcpy(h->d_cs, cs.data(), sizeof(double2) * n, cudaMemcpyHostToDevice));
+    // pm_init (ZHPolar_Match.cpp:68-78): pm_fi[i] = (float)i*dfi + fi_min, pm_si = sinf, pm_co = cosf by the host libm
+    {
+        std::vector<float> fi(n), si(n), co(n);
+        for (int i = 0; i < n; i++) {
+            fi[i] = ((float)i) * laser->dfi + laser->fi_min;
+            si[i] = sinf(fi[i]);
+            co[i] = cosf(fi[i]);
+        }
+        float **dst[3] = {&h->d_fi, &h->d_si, &h->d_co};
+        const float *src[3] = {fi.data(), si.data(), co.data()};
+        for (int k = 0; k < 3; k++) {
+            if (*dst[k]) { cudaFree(*dst[k]); *dst[k] = nullptr; }
+            ZHSM_CUDA_TRY(h, cudaMalloc(dst[k], sizeof(float) * n));
+            ZHSM_CUDA_TRY(h, cudaMemcpy(*dst[k], src[k], sizeof(float) * n, cudaMemcpyHostToDevice));
+        }
+    }
     // GF(2) matrices of the parallel ld_corr_hash for this beam count / CTA shape
     {
         int T, C, ch;
@@ -226,7 +245,7 @@ extern "C" zhsm_status zhsm_median_filter_batch(zhsm_handle *h, float *scans, in
     size_t bytes = sizeof(float) * (size_t)S * n;
     if (!(flags & ZHSM_SCANS_ON_DEVICE)) {
         void *p;
-        zhsm_status s = stage(h, 0, bytes, &p);
+        zhsm_status s = zhsm_stage(h, 0, bytes, &p);
         if (s != ZHSM_OK) return s;
         d = (float *)p;
         ZHSM_CUDA_TRY(h, cudaMemcpyAsync(d, scans, bytes, cudaMemcpyHostToDevice, st));
@@ -291,7 +310,7 @@ extern "C" zhsm_status zhsm_plicp_batch(zhsm_handle *h, const float *scans, int 
     const size_t scan_bytes = sizeof(float) * (size_t)S * n;
     if (flags & ZHSM_SCANS_ON_DEVICE) a.scans = scans;
     else {
-        if ((s = stage(h, 0, scan_bytes, &p)) != ZHSM_OK) return s;
+        if ((s = zhsm_stage(h, 0, scan_bytes, &p)) != ZHSM_OK) return s;
         ZHSM_CUDA_TRY(h, cudaMemcpyAsync(p, scans, scan_bytes, cudaMemcpyHostToDevice, st));
         a.scans = (const float *)p;
     }
@@ -302,13 +321,13 @@ extern "C" zhsm_status zhsm_plicp_batch(zhsm_handle *h, const float *scans, int 
                 h->err = "zhsm_plicp_batch: scan index out of range";
                 return ZHSM_ERR_ARG;
             }
-        if ((s = stage(h, 1, sizeof(int32_t) * 2 * (size_t)B, &p)) != ZHSM_OK) return s;
+        if ((s = zhsm_stage(h, 1, sizeof(int32_t) * 2 * (size_t)B, &p)) != ZHSM_OK) return s;
         int32_t *di = (int32_t *)p;
         ZHSM_CUDA_TRY(h, cudaMemcpyAsync(di, ref_idx, sizeof(int32_t) * B, cudaMemcpyHostToDevice, st));
         ZHSM_CUDA_TRY(h, cudaMemcpyAsync(di + B, sens_idx, sizeof(int32_t) * B, cudaMemcpyHostToDevice, st));
         a.ref_idx = di; a.sens_idx = di + B;
         if (first_guess) {
-            if ((s = stage(h, 2, sizeof(double) * 3 * (size_t)B, &p)) != ZHSM_OK) return s;
+            if ((s = zhsm_stage(h, 2, sizeof(double) * 3 * (size_t)B, &p)) != ZHSM_OK) return s;
             ZHSM_CUDA_TRY(h, cudaMemcpyAsync(p, first_guess, sizeof(double) * 3 * B, cudaMemcpyHostToDevice, st));
             a.first_guess = (const double *)p;
         }
@@ -316,10 +335,10 @@ extern "C" zhsm_status zhsm_plicp_batch(zhsm_handle *h, const float *scans, int 
     const size_t corr_bytes = sizeof(int16_t) * (size_t)B * n;
     if (flags & ZHSM_RESULTS_ON_DEVICE) { a.results = results; a.corr_j1 = corr_j1; a.corr_j2 = corr_j2; }
     else {
-        if ((s = stage(h, 3, sizeof(zhsm_result) * (size_t)B, &p)) != ZHSM_OK) return s;
+        if ((s = zhsm_stage(h, 3, sizeof(zhsm_result) * (size_t)B, &p)) != ZHSM_OK) return s;
         a.results = (zhsm_result *)p;
         if (corr_j1) {
-            if ((s = stage(h, 4, 2 * corr_bytes, &p)) != ZHSM_OK) return s;
+            if ((s = zhsm_stage(h, 4, 2 * corr_bytes, &p)) != ZHSM_OK) return s;
             a.corr_j1 = (int16_t *)p;
             a.corr_j2 = a.corr_j1 + (size_t)B * n;
         }

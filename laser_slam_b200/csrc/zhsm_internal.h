@@ -26,9 +26,11 @@ struct zhsm_handle {
     uint32_t *d_hashmat = nullptr; // GF(2) matrices for the parallel ld_corr_hash, see plicp_sm100.cu
     int hash_chunk = 0, hash_chunks = 0;
 
+    float *d_fi = nullptr, *d_si = nullptr, *d_co = nullptr;  // pm_fi / pm_si / pm_co (pm_init), host libm, float
+
     // staging for host-pointer calls
-    void *d_stage[8] = {nullptr};
-    size_t stage_bytes[8] = {0};
+    void *d_stage[16] = {nullptr};
+    size_t stage_bytes[16] = {0};
 };
 
 // device-side geometry passed by value to kernels
@@ -53,6 +55,24 @@ struct PlicpArgs {
     LaserDev L;
     zhsm_plicp_params P;
 };
+
+struct PsmArgs {
+    const float *scans;          // [S][n] preprocessed ranges (cm)
+    const unsigned char *bad;    // [S][n]
+    const short *seg;            // [S][n]
+    const int32_t *ref_idx, *act_idx;  // [B]
+    const float *init_pose;      // [B][3] act pose (cm, cm, rad) or null
+    zhsm_result *results;        // [B]
+    float *proj_r;               // scan_project mode: [B][n]
+    unsigned char *proj_bad;     // scan_project mode: [B][n]
+    const float *fi, *si, *co;   // [n] host-libm tables (pm_init, ZHPolar_Match.cpp:68-78)
+    int B, algo;
+    LaserDev L;
+};
+cudaError_t psm_launch(const PsmArgs &a, int mode, cudaStream_t st);  // mode 0 matcher, 1 scan_project
+cudaError_t far_segment_launch(const float *scans, unsigned char *bad, short *seg, int S, int n, int max_range_cm,
+                               cudaStream_t st);
+zhsm_status zhsm_stage(zhsm_handle *h, int slot, size_t bytes, void **out);
 
 cudaError_t plicp_launch(const PlicpArgs &a, int sm_count, cudaStream_t st, int *launched);
 // CTA shape the PL-ICP kernel uses for n beams: T threads, C rays per thread, hash chunk (even) per thread

@@ -58,6 +58,7 @@ assert RESULT_DTYPE.itemsize == 128
 
 SCANS_ON_DEVICE, JOBS_ON_DEVICE, RESULTS_ON_DEVICE, ALL_ON_DEVICE = 1, 2, 4, 7
 FILTER_SCANS, WRITEBACK_SCANS = 8, 16
+ALGO_PSM, ALGO_PM_ICP, ALGO_PSM_ICP, ALGO_FMATCH = 0, 1, 2, 3
 
 _lib = None
 
@@ -95,6 +96,10 @@ def load_library():
                                    C.c_ulonglong, vp]
     L.zhsm_fp_peak_tflops.argtypes = [vp, i32]
     L.zhsm_fp_peak_tflops.restype = C.c_double
+    L.zhsm_preprocess_batch.argtypes = [vp, vp, vp, vp, i32, u32, vp]
+    L.zhsm_psm_batch.argtypes = [vp, vp, vp, vp, i32, vp, vp, vp, i32, i32, vp, u32, vp]
+    L.zhsm_scan_project_batch.argtypes = [vp, vp, vp, vp, i32, vp, vp, i32, vp, vp]
+    L.zhsm_debug_libm.argtypes = [vp, i32, vp, vp, vp, i32]
     _lib = L
     return L
 
@@ -195,6 +200,63 @@ class Engine:
         if want_corr:
             return results, j1, j2
         return results
+
+    # ---- zhpsm family (CPolarMatch) -------------------------------------------------------------------------
+    def preprocess(self, scans, bad=None, stream=None):
+        """pm_preprocessScan over a pool: median filter in place, far points, segmentation.
+        Host: numpy float32 [S][n] -> (scans, bad uint8, seg int16).  Device: torch tensors (bad must be given)."""
+        S, n = scans.shape
+        if _is_dev(scans):
+            import torch
+            if bad is None:
+                bad = torch.zeros((S, n), dtype=torch.uint8, device=scans.device)
+            seg = torch.zeros((S, n), dtype=torch.int16, device=scans.device)
+            flags = SCANS_ON_DEVICE
+        else:
+            assert scans.dtype == np.float32 and scans.flags.c_contiguous
+            bad = np.zeros((S, n), np.uint8) if bad is None else np.ascontiguousarray(bad, np.uint8)
+            seg = np.zeros((S, n), np.int16)
+            flags = 0
+        self._check(self.L.zhsm_preprocess_batch(self.h, _ptr(scans), _ptr(bad), _ptr(seg), S, flags, stream),
+                    "zhsm_preprocess_batch")
+        return scans, bad, seg
+
+    def psm(self, scans, bad, seg, ref_idx, act_idx, algo=ALGO_PSM, init_pose=None, results=None, stream=None):
+        """Batched pm_psm / pm_icp / pm_psm->pm_icp / FMatch on preprocessed scans (all arrays on one side)."""
+        dev = _is_dev(scans)
+        dev_jobs = _is_dev(ref_idx)
+        B, S = int(ref_idx.shape[0]), int(scans.shape[0])
+        flags = (SCANS_ON_DEVICE if dev else 0) | (JOBS_ON_DEVICE if dev_jobs else 0)
+        if not dev_jobs:
+            ref_idx = np.ascontiguousarray(ref_idx, np.int32)
+            act_idx = np.ascontiguousarray(act_idx, np.int32)
+            if init_pose is not None:
+                init_pose = np.ascontiguousarray(init_pose, np.float32)
+        if results is None:
+            results = np.zeros(B, RESULT_DTYPE)
+        if _is_dev(results):
+            flags |= RESULTS_ON_DEVICE
+        self._check(self.L.zhsm_psm_batch(self.h, _ptr(scans), _ptr(bad), _ptr(seg), S, _ptr(ref_idx), _ptr(act_idx),
+                                          _ptr(init_pose), B, int(algo), _ptr(results), flags, stream), "zhsm_psm_batch")
+        return results
+
+    def scan_project(self, scans, bad, seg, idx, pose):
+        """pm_scan_project of scans[idx[k]] at pose[k] (host arrays) -> (new_r float32 [B][n], new_bad uint8 [B][n])."""
+        idx = np.ascontiguousarray(idx, np.int32)
+        pose = np.ascontiguousarray(pose, np.float32)
+        B, n = idx.shape[0], scans.shape[1]
+        new_r = np.zeros((B, n), np.float32)
+        new_bad = np.zeros((B, n), np.uint8)
+        self._check(self.L.zhsm_scan_project_batch(self.h, _ptr(scans), _ptr(bad), _ptr(seg), scans.shape[0], _ptr(idx),
+                                                   _ptr(pose), B, _ptr(new_r), _ptr(new_bad)), "zhsm_scan_project_batch")
+        return new_r, new_bad
+
+    def debug_libm(self, which, x, y=None):
+        x = np.ascontiguousarray(x, np.float32)
+        y = np.zeros_like(x) if y is None else np.ascontiguousarray(y, np.float32)
+        out = np.zeros_like(x)
+        self._check(self.L.zhsm_debug_libm(self.h, int(which), _ptr(x), _ptr(y), _ptr(out), x.size), "zhsm_debug_libm")
+        return out
 
     def synth_pairs(self, d_scans, d_truth, first_pair, npairs, dmax_xy_m=0.10, dmax_th_rad=0.0872664626,
                     noise_m=0.01, dropout=0.01, seed=20261104, stream=None):

@@ -1,0 +1,112 @@
+"""GPU parity of the zhpsm family (pm_preprocessScan, pm_scan_project, pm_psm, pm_icp, FMatch) against goldens that
+were produced by EXECUTING the reference's own sources (oracle/_ref, tools/make_goldens.py): parity is pinned.
+
+Everything on this path is float; the device code mirrors the reference's expression shapes, its summation order and
+the host libm's sinf/cosf/atan2f bit for bit, so most results are expected to be IDENTICAL, not merely close.
+Tolerance where a difference is allowed: 1e-2 cm (1e-4 m) and 1e-5 rad, the north star's figures."""
+import ctypes as C
+import zlib
+
+import numpy as np
+import pytest
+
+from laser_slam_b200 import engine as E
+from tests.support import LOGS, load_log, make_laser
+
+pytestmark = pytest.mark.gpu
+
+
+def _crc(a):
+    return zlib.crc32(np.ascontiguousarray(a).tobytes()) & 0xFFFFFFFF
+
+
+def test_device_libm(engine):
+    """csrc/zh_libm.cuh returns the host libm's bits (glibc sinf/cosf/atan2f) on random arguments."""
+    m = C.CDLL("libm.so.6")
+    for f in (m.sinf, m.cosf):
+        f.argtypes = [C.c_float]; f.restype = C.c_float
+    m.atan2f.argtypes = [C.c_float, C.c_float]; m.atan2f.restype = C.c_float
+    rng = np.random.default_rng(5)
+    N = 200000
+    x = rng.uniform(-8, 8, N).astype(np.float32)
+    x[:1000] = rng.uniform(-1e-4, 1e-4, 1000).astype(np.float32)
+    for which, f in ((0, m.sinf), (1, m.cosf)):
+        got = engine.debug_libm(which, x)
+        want = np.array([f(float(v)) for v in x], np.float32)
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), which
+    yy = rng.uniform(-6000, 6000, N).astype(np.float32)
+    xx = rng.uniform(-6000, 6000, N).astype(np.float32)
+    yy[:20000] *= np.float32(1e-3); xx[20000:40000] *= np.float32(1e-3)
+    yy[40000:40100] = 0; xx[40100:40200] = 0; xx[40200:40300] = 1
+    got = engine.debug_libm(2, yy, xx)
+    want = np.array([m.atan2f(float(a), float(b)) for a, b in zip(yy, xx)], np.float32)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+@pytest.fixture(scope="module")
+def pre(engine):
+    cache = {}
+
+    def get(log):
+        if log not in cache:
+            g = load_log(log)
+            engine.set_laser(make_laser(g))
+            r, bad, seg = engine.preprocess(g["scans"].copy())
+            cache[log] = (g, r, bad, seg)
+        else:
+            engine.set_laser(make_laser(cache[log][0]))
+        return cache[log]
+    return get
+
+
+@pytest.mark.parametrize("log", LOGS)
+def test_preprocess_bit_exact(pre, log):
+    g, r, bad, seg = pre(log)
+    for k in range(r.shape[0]):
+        got = [_crc(r[k]), _crc(bad[k].astype(np.int32)), _crc(seg[k].astype(np.int32))]
+        assert got == [int(v) for v in g["pre_crc"][k]], (log, k)
+
+
+@pytest.mark.parametrize("log", LOGS)
+def test_scan_project(engine, pre, log):
+    g, r, bad, seg = pre(log)
+    idx = g["proj_idx"]
+    pose = g["icp_pose"][idx - 1]
+    new_r, new_bad = engine.scan_project(r, bad, seg, idx, pose)
+    same_r = (new_r.view(np.uint32) == g["proj_r"].view(np.uint32)).mean()
+    same_b = (new_bad.astype(np.int8) == g["proj_bad"]).mean()
+    print(f"\n{log}: scan_project bins identical r={same_r:.5f} bad={same_b:.5f}")
+    assert same_b >= 0.999 and same_r >= 0.999
+    assert np.abs(new_r - g["proj_r"])[new_bad.astype(np.int8) == g["proj_bad"]].max() < 1e-2
+
+
+@pytest.mark.parametrize("log", LOGS)
+@pytest.mark.parametrize("name,algo", [("psm", E.ALGO_PSM), ("icp", E.ALGO_PM_ICP), ("psm_icp", E.ALGO_PSM_ICP)])
+def test_matchers_vs_reference_goldens(engine, pre, log, name, algo):
+    g, r, bad, seg = pre(log)
+    S = r.shape[0]
+    res = engine.psm(r, bad, seg, np.arange(S - 1), np.arange(1, S), algo=algo)
+    want_pose, want_st = g[name + "_pose"], g[name + "_status"]
+    st_eq = (res["status"] != 0).astype(np.int8) == want_st
+    ok = want_st == 0
+    got = res["x"].astype(np.float32)
+    ident = (got.view(np.uint32) == want_pose.view(np.uint32)).all(1)
+    d = np.abs(got - want_pose)
+    close = (d[:, 0] <= 1e-2) & (d[:, 1] <= 1e-2) & (d[:, 2] <= 1e-5)
+    print(f"\n{log} {name}: pairs={S-1} status_eq={st_eq.mean():.5f} identical={ident[ok].mean():.5f} "
+          f"within_tol={close[ok].mean():.5f} max|d|={d[ok & st_eq].max(0)}")
+    assert st_eq.mean() >= 0.999
+    assert close[ok & st_eq].mean() >= 0.999
+
+
+@pytest.mark.parametrize("log", ["intel-lab"])
+def test_fmatch_error_index(engine, pre, log):
+    g, r, bad, seg = pre(log)
+    S = 400
+    res = engine.psm(r, bad, seg, np.arange(S - 1), np.arange(1, S), algo=E.ALGO_FMATCH)
+    ok = (g["icp_status"][:S - 1] == 0) & (res["status"] == 0)
+    got = np.stack([res["cov"][:, 0], res["cov"][:, 3]], 1).astype(np.float32)
+    want = g["err_index"][:S - 1]
+    rel = np.abs(got - want) / np.maximum(np.abs(want), 1e-12)
+    print(f"\n{log}: pm_error_index2 identical={(got == want)[ok].all(1).mean():.5f} max rel={rel[ok].max():.3g}")
+    assert (rel[ok].max(1) < 1e-3).mean() >= 0.999
