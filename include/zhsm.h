@@ -162,6 +162,45 @@ zhsm_status zhsm_psm_batch(zhsm_handle *h, const float *scans, const uint8_t *ba
 zhsm_status zhsm_scan_project_batch(zhsm_handle *h, const float *scans, const uint8_t *bad, const int16_t *seg, int S,
                                     const int32_t *idx, const float *pose, int B, float *new_r, uint8_t *new_bad);
 
+/* ---- zhicp: point-to-point ICP (src/zhicp/ZHIcp_Warpper.cpp -> mrpt::slam::CICP, icpClassic) ---------------------
+ * Options of mrpt::slam::CICP::TConfigParams the path reads.  zhsm_icp_default_options() fills the values
+ * CICPWarpper::initICP sets (ZHIcp_Warpper.cpp:43-53) and MRPT's defaults for the rest. */
+typedef struct zhsm_icp_options {
+    int32_t maxIterations;              /* 100 (:46) */
+    float thresholdAng;                 /* DEG2RAD(10) (:47) */
+    float thresholdDist;                /* 0.75 (:48) */
+    float ALFA;                         /* 0.5 (:49) */
+    float smallestThresholdDist;        /* 0.05 (:50) */
+    int32_t onlyClosestCorrespondences; /* 1 */
+    float minAbsStep_trans;             /* 1e-6 */
+    float minAbsStep_rot;               /* 1e-6 */
+    int32_t corresponding_points_decimation; /* 5 */
+    int32_t rotate_decimation_offset;   /* 0 never, 1 every iteration, 2 whenever the thresholds shrink (default) */
+    float kernel_rho;                   /* 0.07 */
+    int32_t use_kernel;                 /* 1 */
+    float Axy_aprox_derivatives;        /* 0.05 */
+} zhsm_icp_options;
+
+void zhsm_icp_default_options(zhsm_icp_options *o);
+
+/* Batched CICPWarpper::ICPMatch (ZHIcp_Warpper.cpp:125-176).  Point clouds live in a cloud pool: cloud c has cnt[c]
+ * points stored at pts[2*off[c]] as x[0..cnt) followed by y[0..cnt) (metres, float32: the rx/ry, ax/ay arrays the
+ * wrapper receives).  off/cnt ([C], HOST arrays always) are the pool's table of contents; pts is [2*npts] and may be
+ * device memory (ZHSM_SCANS_ON_DEVICE).  Job k aligns cloud cur_idx[k] to the map cloud ref_idx[k] from the initial
+ * guess init[k] ([B][3] doubles m,m,rad, NULL = zeros); a multi-start batch lists a pair G times with G guesses.
+ * Per job: results[k].x = pose (getResult, :188-206), .cov = upper triangle of the 3x3 covariance, .iterations /
+ * .goodness / .quality = getMatchQuality (:208-213), .nvalid = correspondences of the last iteration; .valid = 0
+ * when no correspondence was found.  The value ICPMatch returns is .goodness. */
+zhsm_status zhsm_icp_batch(zhsm_handle *h, const float *pts, long long npts, const int32_t *off, const int32_t *cnt,
+                           int C, const int32_t *ref_idx, const int32_t *cur_idx, const double *init, int B,
+                           const zhsm_icp_options *opt, zhsm_result *results, unsigned flags, void *cuda_stream);
+
+/* Multi-start reduction: results holds P pairs x G starts (pair-major).  best[p] = the start with the highest
+ * goodness among the valid ones (ties: lowest start index; -1 if none), best_results[p] = its record.  Either
+ * output may be NULL.  ZHSM_RESULTS_ON_DEVICE covers results, best and best_results. */
+zhsm_status zhsm_best_of_starts(zhsm_handle *h, const zhsm_result *results, int P, int G, int32_t *best,
+                                zhsm_result *best_results, unsigned flags, void *cuda_stream);
+
 /* blocks until everything queued on the handle's stream (or the given one) is done */
 zhsm_status zhsm_sync(zhsm_handle *h, void *cuda_stream);
 

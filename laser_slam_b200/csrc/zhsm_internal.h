@@ -72,6 +72,19 @@ struct PsmArgs {
 cudaError_t psm_launch(const PsmArgs &a, int mode, cudaStream_t st);  // mode 0 matcher, 1 scan_project
 cudaError_t far_segment_launch(const float *scans, unsigned char *bad, short *seg, int S, int n, int max_range_cm,
                                cudaStream_t st);
+struct IcpArgs {
+    const float *pts;            // cloud pool, x-block then y-block per cloud
+    const int32_t *off, *cnt;    // [C] device copies of the pool's table of contents
+    const int32_t *ref_idx, *cur_idx;  // [B]
+    const double *init;          // [B][3] or null
+    zhsm_result *results;        // [B]
+    int B, cap;                  // cap = capacity (points) of the shared-memory arrays = largest cloud
+    zhsm_icp_options opt;
+};
+cudaError_t icp_launch(const IcpArgs &a, cudaStream_t st);
+size_t icp_smem_bytes(int cap);
+cudaError_t best_of_starts_launch(const zhsm_result *results, int P, int G, int32_t *best, zhsm_result *best_results,
+                                  cudaStream_t st);
 zhsm_status zhsm_stage(zhsm_handle *h, int slot, size_t bytes, void **out);
 
 cudaError_t plicp_launch(const PlicpArgs &a, int sm_count, cudaStream_t st, int *launched);

@@ -51,6 +51,15 @@ class PlicpParams(C.Structure):
                                  "outliers_remove_doubles", "do_compute_covariance")] + [("reserved", C.c_int32 * 2)]
 
 
+class IcpOptions(C.Structure):
+    """zhsm_icp_options (include/zhsm.h): mrpt::slam::CICP::TConfigParams as CICPWarpper::initICP sets them."""
+    _fields_ = [("maxIterations", C.c_int32), ("thresholdAng", C.c_float), ("thresholdDist", C.c_float),
+                ("ALFA", C.c_float), ("smallestThresholdDist", C.c_float), ("onlyClosestCorrespondences", C.c_int32),
+                ("minAbsStep_trans", C.c_float), ("minAbsStep_rot", C.c_float),
+                ("corresponding_points_decimation", C.c_int32), ("rotate_decimation_offset", C.c_int32),
+                ("kernel_rho", C.c_float), ("use_kernel", C.c_int32), ("Axy_aprox_derivatives", C.c_float)]
+
+
 RESULT_DTYPE = np.dtype([("x", "f8", 3), ("cov", "f8", 6), ("error", "f8"), ("valid", "i4"), ("iterations", "i4"),
                          ("nvalid", "i4"), ("status", "i4"), ("goodness", "f4"), ("quality", "f4"),
                          ("corr_hash", "u4"), ("n_loops", "i4"), ("reserved", "i4", 4)])
@@ -100,6 +109,10 @@ def load_library():
     L.zhsm_psm_batch.argtypes = [vp, vp, vp, vp, i32, vp, vp, vp, i32, i32, vp, u32, vp]
     L.zhsm_scan_project_batch.argtypes = [vp, vp, vp, vp, i32, vp, vp, i32, vp, vp]
     L.zhsm_debug_libm.argtypes = [vp, i32, vp, vp, vp, i32]
+    L.zhsm_icp_default_options.argtypes = [C.POINTER(IcpOptions)]
+    L.zhsm_icp_default_options.restype = None
+    L.zhsm_icp_batch.argtypes = [vp, vp, C.c_longlong, vp, vp, i32, vp, vp, vp, i32, C.POINTER(IcpOptions), vp, u32, vp]
+    L.zhsm_best_of_starts.argtypes = [vp, vp, i32, i32, vp, vp, u32, vp]
     _lib = L
     return L
 
@@ -250,6 +263,52 @@ class Engine:
         self._check(self.L.zhsm_scan_project_batch(self.h, _ptr(scans), _ptr(bad), _ptr(seg), scans.shape[0], _ptr(idx),
                                                    _ptr(pose), B, _ptr(new_r), _ptr(new_bad)), "zhsm_scan_project_batch")
         return new_r, new_bad
+
+    def default_icp_options(self, **over):
+        o = IcpOptions()
+        self.L.zhsm_icp_default_options(C.byref(o))
+        for k, v in over.items():
+            setattr(o, k, v)
+        return o
+
+    def icp(self, pts, off, cnt, ref_idx, cur_idx, init=None, options=None, results=None, stream=None):
+        """Batched CICPWarpper::ICPMatch over a cloud pool (see zhsm_icp_batch).  off/cnt are host int32 arrays;
+        pts / the job arrays / results may each be numpy (host) or torch CUDA tensors."""
+        off = np.ascontiguousarray(off, np.int32)
+        cnt = np.ascontiguousarray(cnt, np.int32)
+        flags = (SCANS_ON_DEVICE if _is_dev(pts) else 0) | (JOBS_ON_DEVICE if _is_dev(ref_idx) else 0)
+        if not _is_dev(pts):
+            pts = np.ascontiguousarray(pts, np.float32)
+        if not _is_dev(ref_idx):
+            ref_idx = np.ascontiguousarray(ref_idx, np.int32)
+            cur_idx = np.ascontiguousarray(cur_idx, np.int32)
+            if init is not None:
+                init = np.ascontiguousarray(init, np.float64)
+        B = int(ref_idx.shape[0])
+        npts = int(pts.shape[0]) // 2
+        if results is None:
+            results = np.zeros(B, RESULT_DTYPE)
+        if _is_dev(results):
+            flags |= RESULTS_ON_DEVICE
+        self._check(self.L.zhsm_icp_batch(self.h, _ptr(pts), npts, _ptr(off), _ptr(cnt), int(off.size), _ptr(ref_idx),
+                                          _ptr(cur_idx), _ptr(init), B, C.byref(options) if options is not None else None,
+                                          _ptr(results), flags, stream), "zhsm_icp_batch")
+        return results
+
+    def best_of_starts(self, results, P, G, stream=None):
+        """Per pair the start with the highest goodness: returns (best index [P], best record [P])."""
+        if _is_dev(results):
+            import torch
+            best = torch.empty(P, dtype=torch.int32, device=results.device)
+            rec = torch.empty((P, 128), dtype=torch.uint8, device=results.device)
+            flags = RESULTS_ON_DEVICE
+        else:
+            best = np.zeros(P, np.int32)
+            rec = np.zeros(P, RESULT_DTYPE)
+            flags = 0
+        self._check(self.L.zhsm_best_of_starts(self.h, _ptr(results), int(P), int(G), _ptr(best), _ptr(rec), flags,
+                                               stream), "zhsm_best_of_starts")
+        return best, rec
 
     def debug_libm(self, which, x, y=None):
         x = np.ascontiguousarray(x, np.float32)

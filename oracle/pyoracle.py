@@ -264,3 +264,59 @@ def _f32(a):
 
 def _i32(a):
     return np.ascontiguousarray(a, np.int32)
+
+
+# ---------------------------------------------------------------------------------------------
+# zhicp: MRPT 0.9.6 CICP (classic) restatement, oracle/icp_oracle.c  -- PARITY UNPINNED
+# ---------------------------------------------------------------------------------------------
+class IcpOptions(C.Structure):
+    _fields_ = [("maxIterations", C.c_int), ("thresholdAng", C.c_float), ("thresholdDist", C.c_float),
+                ("ALFA", C.c_float), ("smallestThresholdDist", C.c_float), ("onlyClosestCorrespondences", C.c_int),
+                ("minAbsStep_trans", C.c_float), ("minAbsStep_rot", C.c_float),
+                ("corresponding_points_decimation", C.c_int), ("rotate_decimation_offset", C.c_int),
+                ("kernel_rho", C.c_float), ("use_kernel", C.c_int), ("Axy_aprox_derivatives", C.c_float)]
+
+
+ICP_RESULT_DTYPE = np.dtype([("pose", "f8", 3), ("cov", "f8", 9), ("nIterations", "i4"), ("nCorrespondences", "i4"),
+                             ("goodness", "f4"), ("quality", "f4")])
+
+
+def icp_default_options(**over):
+    o = IcpOptions()
+    lib().orc_icp_default_options.argtypes = [C.POINTER(IcpOptions)]
+    lib().orc_icp_default_options(C.byref(o))
+    for k, v in over.items():
+        setattr(o, k, v)
+    return o
+
+
+def pack_clouds(clouds):
+    """list of (x[N], y[N]) -> (pts float32 [2*sum N] as x-block then y-block per cloud, off int32, cnt int32)."""
+    cnt = np.array([len(c[0]) for c in clouds], np.int32)
+    off = np.zeros(len(clouds), np.int32)
+    off[1:] = np.cumsum(cnt)[:-1]
+    pts = np.zeros(2 * int(cnt.sum()), np.float32)
+    for k, (x, y) in enumerate(clouds):
+        o, n = 2 * int(off[k]), int(cnt[k])
+        pts[o:o + n] = x
+        pts[o + n:o + 2 * n] = y
+    return pts, off, cnt
+
+
+def mrpt_icp_batch(pts, off, cnt, ref_idx, cur_idx, init, options=None, nthreads=1):
+    """CICPWarpper::ICPMatch for every job k: clouds ref_idx[k] (map) and cur_idx[k], initial guess init[k]."""
+    pts = np.ascontiguousarray(pts, np.float32)
+    off = np.ascontiguousarray(off, np.int32)
+    cnt = np.ascontiguousarray(cnt, np.int32)
+    ri = np.ascontiguousarray(ref_idx, np.int32)
+    ci = np.ascontiguousarray(cur_idx, np.int32)
+    init = np.ascontiguousarray(init, np.float64).reshape(-1, 3)
+    assert init.shape[0] == ri.size == ci.size
+    out = np.zeros(ri.size, ICP_RESULT_DTYPE)
+    assert ICP_RESULT_DTYPE.itemsize == 112
+    L = lib()
+    L.orc_mrpt_icp_batch.argtypes = [C.c_void_p] * 6 + [C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+    L.orc_mrpt_icp_batch(pts.ctypes.data, off.ctypes.data, cnt.ctypes.data, ri.ctypes.data, ci.ctypes.data,
+                         init.ctypes.data, ri.size, C.byref(options) if options is not None else None,
+                         out.ctypes.data, int(nthreads))
+    return out

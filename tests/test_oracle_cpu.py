@@ -216,3 +216,69 @@ def test_compiled_reference_reproduces_zhpsm_goldens(log):
             assert st == int(g[name + "_status"][k])
             if st == 0:
                 assert np.array_equal(pose, g[name + "_pose"][k]), (name, k)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# zhicp oracle (oracle/icp_oracle.c): PARITY UNPINNED (MRPT 0.9.6 absent) -- pinned against regressions by the frozen
+# outputs on the reference's own wrapper-test clouds, and checked for the properties the algorithm must have.
+# ---------------------------------------------------------------------------------------------------------------
+def _icp_nodes():
+    import os
+    return np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "zhicp_nodes.npz"))
+
+
+def test_icp_oracle_matches_frozen_outputs():
+    d = _icp_nodes()
+    r = po.mrpt_icp_batch(d["pts"], d["off"], d["cnt"], d["pairs"][:, 0], d["pairs"][:, 1], d["init"], nthreads=4)
+    g = d["oracle"]
+    assert np.array_equal(r["nIterations"], g["nIterations"])
+    assert np.array_equal(r["nCorrespondences"], g["nCorrespondences"])
+    assert np.allclose(r["pose"], g["pose"], rtol=0, atol=1e-12)
+    assert np.allclose(r["goodness"], g["goodness"]) and np.allclose(r["quality"], g["quality"], atol=1e-6)
+
+
+def test_icp_oracle_goodness_consistent_with_reference_logging_rule():
+    """src/mapGraph/MapGraph.cpp:1385-1394 logs a pair to data/matched_nodes.log only when the reference's own ICP
+    returned 0.4 < goodness < 0.8 (ICP_QUALITY_THRESHOLD, :42); data2's pairs were logged on acceptance (:1586-1590).
+    The restatement, run on those very clouds and guesses, must land in the same bands for almost all of them --
+    the only behavioural evidence about MRPT's numbers that the reference tree holds."""
+    d = _icp_nodes()
+    g = d["oracle"]["goodness"]
+    names = d["names"][d["pairs"][:, 0]]
+    first = np.array([n.startswith("data/") for n in names])
+    rejected, accepted = g[first], g[~first]
+    assert ((rejected > 0.4) & (rejected < 0.8)).mean() >= 0.9, rejected
+    assert (accepted >= 0.8).all(), accepted
+
+
+def test_icp_oracle_recovers_a_known_transform():
+    rng = np.random.default_rng(3)
+    # scattered landmarks (point-to-point ICP slides along evenly sampled walls, so walls alone cannot pin a pose)
+    x = rng.uniform(0, 6, 400).astype(np.float32)
+    y = rng.uniform(0, 6, 400).astype(np.float32)
+    for tx, ty, th in ((0.12, -0.08, 0.05), (-0.2, 0.15, -0.08), (0, 0, 0)):
+        c, s = np.cos(th), np.sin(th)
+        # current cloud = map seen from pose (tx,ty,th): p_cur = R^T (p_map - t)
+        cx = (c * (x - tx) + s * (y - ty)).astype(np.float32)
+        cy = (-s * (x - tx) + c * (y - ty)).astype(np.float32)
+        pts, off, cnt = po.pack_clouds([(x, y), (cx, cy)])
+        r = po.mrpt_icp_batch(pts, off, cnt, [0], [1], np.zeros((1, 3)),
+                              po.icp_default_options(corresponding_points_decimation=1))[0]
+        assert abs(r["pose"][0] - tx) < 5e-3 and abs(r["pose"][1] - ty) < 5e-3 and abs(r["pose"][2] - th) < 2e-3, r
+        assert r["goodness"] > 0.95 and 1 < r["nIterations"] <= 100
+        assert np.all(np.linalg.eigvalsh(r["cov"].reshape(3, 3)) > 0)
+
+
+def test_icp_oracle_threshold_schedule():
+    """The loop shrinks the gate by ALFA each time the pose stops moving and ends when it falls under
+    smallestThresholdDist: identical clouds need exactly ceil(log(0.05/0.75)/log(0.5)) = 4 iterations at
+    zero guess (every iteration is a no-move), and maxIterations is a hard cap only while the gate is small."""
+    a = np.arange(0, 4, 0.05, dtype=np.float32)
+    pts, off, cnt = po.pack_clouds([(a, a * 0.3), (a, a * 0.3)])
+    r = po.mrpt_icp_batch(pts, off, cnt, [0], [1], np.zeros((1, 3)),
+                          po.icp_default_options(corresponding_points_decimation=1))[0]
+    assert r["nIterations"] == 4 and r["goodness"] == 1.0 and np.allclose(r["pose"], 0, atol=1e-7)
+    r = po.mrpt_icp_batch(pts, off, cnt, [0], [1], np.zeros((1, 3)),
+                          po.icp_default_options(corresponding_points_decimation=1, maxIterations=2))[0]
+    # after 2 iterations the gate (0.1875) is still above 0.05: the tail rule keeps halving and iterating
+    assert r["nIterations"] > 2
