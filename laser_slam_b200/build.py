@@ -63,7 +63,7 @@ def build_host(verbose=False):
     root = os.path.dirname(HERE)
     host = os.path.join(HERE, "host")
     out = os.path.join(HERE, "libzhsm_host.so")
-    srcs = [os.path.join(host, "ZHCanonical_Matcher.cpp")]
+    srcs = [os.path.join(host, f) for f in ("ZHCanonical_Matcher.cpp", "ZHPolar_Match.cpp", "ZHIcp_Warpper.cpp")]
     deps = srcs + [os.path.join(host, f) for f in os.listdir(host) if f.endswith(".h")] + [os.path.join(root, "include", "zhsm.h")]
     cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
     if not os.path.exists(out) or os.path.getmtime(out) < newest(deps):
@@ -74,11 +74,13 @@ def build_host(verbose=False):
     bdir = os.path.join(tdir, "_build")
     os.makedirs(bdir, exist_ok=True)
     exe = os.path.join(bdir, "shim_runlog")
-    src = os.path.join(tdir, "shim_runlog.cpp")
-    if not os.path.exists(exe) or os.path.getmtime(exe) < newest(deps + [src, out]):
-        cmd = [cxx, "-O2", "-std=c++17", "-Wall", "-I" + os.path.join(root, "include"), "-I" + host, "-o", exe, src,
-               "-L" + HERE, "-lzhsm_host", "-lzhsm", "-Wl,-rpath," + HERE]
-        subprocess.run(cmd, check=True)
+    for name in ("shim_runlog", "shim_icp"):
+        exe_k = os.path.join(bdir, name)
+        src = os.path.join(tdir, name + ".cpp")
+        if not os.path.exists(exe_k) or os.path.getmtime(exe_k) < newest(deps + [src, out]):
+            cmd = [cxx, "-O2", "-std=c++17", "-Wall", "-I" + os.path.join(root, "include"), "-I" + host, "-o", exe_k, src,
+                   "-L" + HERE, "-lzhsm_host", "-lzhsm", "-Wl,-rpath," + HERE]
+            subprocess.run(cmd, check=True)
     return out, exe
 
 
