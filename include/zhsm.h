@@ -162,6 +162,11 @@ zhsm_status zhsm_psm_batch(zhsm_handle *h, const float *scans, const uint8_t *ba
 zhsm_status zhsm_scan_project_batch(zhsm_handle *h, const float *scans, const uint8_t *bad, const int16_t *seg, int S,
                                     const int32_t *idx, const float *pose, int B, float *new_r, uint8_t *new_bad);
 
+/* pm_is_corridor (:2058-2186) over S preprocessed scans: out[k] = 1 corridor, 0 room, -3 / -2 where the reference
+ * throws 3 / 2 (fewer than two usable line directions).  out is a host array unless ZHSM_RESULTS_ON_DEVICE. */
+zhsm_status zhsm_is_corridor_batch(zhsm_handle *h, const float *scans, const uint8_t *bad, const int16_t *seg, int S,
+                                   int8_t *out, unsigned flags, void *cuda_stream);
+
 /* ---- zhicp: point-to-point ICP (src/zhicp/ZHIcp_Warpper.cpp -> mrpt::slam::CICP, icpClassic) ---------------------
  * Options of mrpt::slam::CICP::TConfigParams the path reads.  zhsm_icp_default_options() fills the values
  * CICPWarpper::initICP sets (ZHIcp_Warpper.cpp:43-53) and MRPT's defaults for the rest. */
@@ -189,17 +194,21 @@ void zhsm_icp_default_options(zhsm_icp_options *o);
  * device memory (ZHSM_SCANS_ON_DEVICE).  Job k aligns cloud cur_idx[k] to the map cloud ref_idx[k] from the initial
  * guess init[k] ([B][3] doubles m,m,rad, NULL = zeros); a multi-start batch lists a pair G times with G guesses.
  * Per job: results[k].x = pose (getResult, :188-206), .cov = upper triangle of the 3x3 covariance, .iterations /
- * .goodness / .quality = getMatchQuality (:208-213), .nvalid = correspondences of the last iteration; .valid = 0
- * when no correspondence was found.  The value ICPMatch returns is .goodness. */
+ * .goodness / .quality = getMatchQuality (:208-213), .nvalid = correspondences of the last iteration, .error = their
+ * mean squared distance (an extra; MRPT does not report it); .valid = 0 when no correspondence was found.  The value ICPMatch returns is .goodness. */
 zhsm_status zhsm_icp_batch(zhsm_handle *h, const float *pts, long long npts, const int32_t *off, const int32_t *cnt,
                            int C, const int32_t *ref_idx, const int32_t *cur_idx, const double *init, int B,
                            const zhsm_icp_options *opt, zhsm_result *results, unsigned flags, void *cuda_stream);
 
-/* Multi-start reduction: results holds P pairs x G starts (pair-major).  best[p] = the start with the highest
- * goodness among the valid ones (ties: lowest start index; -1 if none), best_results[p] = its record.  Either
- * output may be NULL.  ZHSM_RESULTS_ON_DEVICE covers results, best and best_results. */
-zhsm_status zhsm_best_of_starts(zhsm_handle *h, const zhsm_result *results, int P, int G, int32_t *best,
-                                zhsm_result *best_results, unsigned flags, void *cuda_stream);
+/* Multi-start reduction: results holds P pairs x G starts (pair-major).  best[p] = the preferred start among the
+ * valid ones (-1 if none), best_results[p] = its record.  criterion ZHSM_BEST_GOODNESS (zhicp: highest goodness, then
+ * lowest .error, then lowest start index -- the callers' acceptance is a goodness threshold, MapGraph.cpp:42,1385) or
+ * ZHSM_BEST_MEAN_ERROR (PL-ICP: lowest error / nvalid, then lowest start index).  Either output may be NULL.
+ * ZHSM_RESULTS_ON_DEVICE covers results, best and best_results. */
+#define ZHSM_BEST_GOODNESS 0
+#define ZHSM_BEST_MEAN_ERROR 1
+zhsm_status zhsm_best_of_starts(zhsm_handle *h, const zhsm_result *results, int P, int G, int criterion,
+                                int32_t *best, zhsm_result *best_results, unsigned flags, void *cuda_stream);
 
 /* blocks until everything queued on the handle's stream (or the given one) is done */
 zhsm_status zhsm_sync(zhsm_handle *h, void *cuda_stream);

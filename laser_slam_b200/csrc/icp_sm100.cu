@@ -276,9 +276,14 @@ __global__ void __launch_bounds__(T) icp_kernel(IcpArgs a) {
         } while ((keep && nIter < o.maxIterations) || (nIter >= o.maxIterations && umbral_dist > o.smallestThresholdDist));
     }
 
-    double cov[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    double cov[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, mse = 0;
     float quality = 0, goodness = 1;
     if (nCorr) {
+        if (t == 0) {  // not part of the wrapper's interface: mean squared distance of the final correspondences
+            double sum = 0;
+            for (int k = 0; k < nCorr; k++) sum += s.qd[s.list[k]];
+            mse = sum / nCorr;
+        }
         // covariance (D D^T + 1e-6 I)^-1; D = three-point numerical derivative of the (kernelised) squared residuals
         const double ccos = cos(mphi), csin = sin(mphi);
         const double Axy = o.Axy_aprox_derivatives, rho2 = (double)o.kernel_rho * o.kernel_rho;
@@ -357,20 +362,27 @@ __global__ void __launch_bounds__(T) icp_kernel(IcpArgs a) {
         r.nvalid = nCorr;
         r.goodness = goodness;
         r.quality = quality;
+        r.error = mse;
         a.results[job] = r;
     }
 }
 
-// Multi-start reduction: for pair p the best of its G jobs results[p*G .. p*G+G): highest goodness,
-// ties to the lower start index (the order a sequential caller would try them).  One thread per pair.
-__global__ void best_of_starts_kernel(const zhsm_result *results, int P, int G, int32_t *best, zhsm_result *best_results) {
+// Multi-start reduction: for pair p the best of its G jobs results[p*G .. p*G+G).
+//   criterion 0 (zhicp):  highest goodness, then lowest error, then lowest start index
+//   criterion 1 (PL-ICP): lowest error per valid correspondence (sm_result.error / nvalid), then lowest start index
+// -- the order a sequential caller trying the starts one after the other would prefer them.  One thread per pair.
+__global__ void best_of_starts_kernel(const zhsm_result *results, int P, int G, int criterion, int32_t *best,
+                                      zhsm_result *best_results) {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= P) return;
     int bi = -1;
-    float bg = -FLT_MAX;
+    double bk0 = 0, bk1 = 0;
     for (int g = 0; g < G; g++) {
         const zhsm_result &r = results[(size_t)p * G + g];
-        if (r.valid && r.goodness > bg) { bg = r.goodness; bi = g; }
+        if (!r.valid) continue;
+        const double k0 = criterion == 0 ? -(double)r.goodness : r.error / (double)(r.nvalid > 0 ? r.nvalid : 1);
+        const double k1 = criterion == 0 ? r.error : 0.0;
+        if (bi < 0 || k0 < bk0 || (k0 == bk0 && k1 < bk1)) { bi = g; bk0 = k0; bk1 = k1; }
     }
     if (best) best[p] = bi;
     if (best_results) {
@@ -391,8 +403,8 @@ cudaError_t icp_launch(const IcpArgs &a, cudaStream_t st) {
     return cudaGetLastError();
 }
 
-cudaError_t best_of_starts_launch(const zhsm_result *results, int P, int G, int32_t *best, zhsm_result *best_results,
-                                  cudaStream_t st) {
-    icp::best_of_starts_kernel<<<(P + 127) / 128, 128, 0, st>>>(results, P, G, best, best_results);
+cudaError_t best_of_starts_launch(const zhsm_result *results, int P, int G, int criterion, int32_t *best,
+                                  zhsm_result *best_results, cudaStream_t st) {
+    icp::best_of_starts_kernel<<<(P + 127) / 128, 128, 0, st>>>(results, P, G, criterion, best, best_results);
     return cudaGetLastError();
 }

@@ -107,7 +107,67 @@ __global__ void far_segment_kernel(const float *scans, unsigned char *bad, short
     }
 }
 
+// pm_is_corridor (ZHPolar_Match.cpp:2058-2186): standard deviation of the (3-tap median filtered) directions of the
+// lines through neighbouring points of a segment, computed twice (the second time rotated by pi/5, without the median:
+// the reference's second window assignment order makes all three taps equal).  Sequential float sums: one thread
+// walks one scan.  out: 1 corridor, 0 room, -3 / -2 = the reference's `throw 3` / `throw 2` (fewer than 2 lines).
+__global__ void corridor_kernel(const float *scans, const unsigned char *bad, const short *seg, const float *fi_t,
+                                const float *si_t, const float *co_t, int S, int n, signed char *out) {
+    const int sidx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (sidx >= S) return;
+    const float *r = scans + (size_t)sidx * n;
+    const unsigned char *b = bad + (size_t)sidx * n;
+    const short *sg = seg + (size_t)sidx * n;
+    const double R2D = 180.0 / PI_BODY;
+    float fi1 = 0, fi2 = 0, fi3 = 0, sxx = 0, sx = 0, cnt = 0, std1, std2;
+    for (int i = 0; i < n - 1; i++) {
+        if (sg[i] == sg[i + 1] && sg[i] != 0 && !b[i]) {
+            const float x = r[i] * co_t[i], y = r[i] * si_t[i];
+            const float x1 = r[i + 1] * co_t[i + 1], y1 = r[i + 1] * si_t[i + 1];
+            float fi = (float)((double)zhm::atan2f_glibc(y1 - y, x1 - x) * R2D);
+            if (fi < 0) fi = (float)((double)fi + 180.0);
+            if (i == 0) { fi1 = fi; fi2 = fi; fi3 = fi; }
+            fi3 = fi2; fi2 = fi1; fi1 = fi;
+            if (fi1 <= fi2 && fi2 <= fi3) fi = fi2;
+            if (fi2 <= fi3 && fi3 <= fi1) fi = fi3;
+            if (fi3 <= fi1 && fi1 <= fi2) fi = fi1;
+            sx += fi;
+            sxx += fi * fi;
+            cnt = (float)((double)cnt + 1.0);
+        }
+    }
+    if (cnt > 1) {
+        const float var = (float)((double)(sxx - sx * sx / cnt) / ((double)cnt - 1.0));
+        std1 = var > 0 ? sqrtf(var) : 0.f;
+    } else { out[sidx] = -3; return; }
+    sxx = 0; cnt = 0; sx = 0;
+    for (int i = 0; i < n - 1; i++) {
+        if (sg[i] == sg[i + 1] && sg[i] != 0 && !b[i]) {
+            const float a0 = (float)((double)fi_t[i] + PI_BODY / 5.0), a1 = (float)((double)fi_t[i + 1] + PI_BODY / 5.0);
+            const float x = r[i] * zhm::cosf_glibc(a0), y = r[i] * zhm::sinf_glibc(a0);
+            const float x1 = r[i + 1] * zhm::cosf_glibc(a1), y1 = r[i + 1] * zhm::sinf_glibc(a1);
+            float fi = (float)((double)zhm::atan2f_glibc(y1 - y, x1 - x) * R2D);
+            if (fi < 0) fi = (float)((double)fi + 180.0);
+            sx += fi;
+            sxx += fi * fi;
+            cnt = (float)((double)cnt + 1.0);
+        }
+    }
+    if (cnt > 1) {
+        const float var = (float)((double)(sxx - sx * sx / cnt) / ((double)cnt - 1.0));
+        std2 = var > 0 ? sqrtf(var) : 0.f;
+    } else { out[sidx] = -2; return; }
+    const float st = std1 < std2 ? std1 : std2;
+    out[sidx] = st < 25.0f ? 1 : 0;  // PM_CORRIDOR_THRESHOLD (PolarParameter.h:24)
+}
+
 }  // namespace psm
+
+cudaError_t corridor_launch(const float *scans, const unsigned char *bad, const short *seg, const float *fi,
+                            const float *si, const float *co, int S, int n, signed char *out, cudaStream_t st) {
+    psm::corridor_kernel<<<(S + 63) / 64, 64, 0, st>>>(scans, bad, seg, fi, si, co, S, n, out);
+    return cudaGetLastError();
+}
 
 cudaError_t psm_launch(const psm::Args &a, int mode, cudaStream_t st) {
     const size_t smem = psm::sh_bytes(a.L.n);

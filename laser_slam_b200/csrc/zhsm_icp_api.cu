@@ -101,15 +101,15 @@ extern "C" zhsm_status zhsm_icp_batch(zhsm_handle *h, const float *pts, long lon
     return ZHSM_OK;
 }
 
-extern "C" zhsm_status zhsm_best_of_starts(zhsm_handle *h, const zhsm_result *results, int P, int G, int32_t *best,
-                                           zhsm_result *best_results, unsigned flags, void *cuda_stream) {
+extern "C" zhsm_status zhsm_best_of_starts(zhsm_handle *h, const zhsm_result *results, int P, int G, int criterion,
+                                           int32_t *best, zhsm_result *best_results, unsigned flags, void *cuda_stream) {
     if (!h) return ZHSM_ERR_ARG;
-    if (!results || P < 0 || G < 1 || (!best && !best_results)) { h->err = "zhsm_best_of_starts: bad argument"; return ZHSM_ERR_ARG; }
+    if (!results || P < 0 || G < 1 || criterion < 0 || criterion > 1 || (!best && !best_results)) { h->err = "zhsm_best_of_starts: bad argument"; return ZHSM_ERR_ARG; }
     if (P == 0) return ZHSM_OK;
     ZHSM_CUDA_TRY(h, cudaSetDevice(h->device));
     cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : h->stream;
     if (flags & ZHSM_RESULTS_ON_DEVICE) {
-        ZHSM_CUDA_TRY(h, best_of_starts_launch(results, P, G, best, best_results, st));
+        ZHSM_CUDA_TRY(h, best_of_starts_launch(results, P, G, criterion, best, best_results, st));
         h->launches++;
         return ZHSM_OK;
     }
@@ -123,7 +123,7 @@ extern "C" zhsm_status zhsm_best_of_starts(zhsm_handle *h, const zhsm_result *re
     if ((s = zhsm_stage(h, 13, sizeof(int32_t) * (size_t)P, &p)) != ZHSM_OK) return s;
     int32_t *dbest = (int32_t *)p;
     ZHSM_CUDA_TRY(h, cudaMemcpyAsync(din, results, nin, cudaMemcpyHostToDevice, st));
-    ZHSM_CUDA_TRY(h, best_of_starts_launch(din, P, G, dbest, dout, st));
+    ZHSM_CUDA_TRY(h, best_of_starts_launch(din, P, G, criterion, dbest, dout, st));
     h->launches++;
     if (best) ZHSM_CUDA_TRY(h, cudaMemcpyAsync(best, dbest, sizeof(int32_t) * (size_t)P, cudaMemcpyDeviceToHost, st));
     if (best_results) ZHSM_CUDA_TRY(h, cudaMemcpyAsync(best_results, dout, sizeof(zhsm_result) * (size_t)P, cudaMemcpyDeviceToHost, st));

@@ -83,8 +83,10 @@ struct IcpArgs {
 };
 cudaError_t icp_launch(const IcpArgs &a, cudaStream_t st);
 size_t icp_smem_bytes(int cap);
-cudaError_t best_of_starts_launch(const zhsm_result *results, int P, int G, int32_t *best, zhsm_result *best_results,
-                                  cudaStream_t st);
+cudaError_t best_of_starts_launch(const zhsm_result *results, int P, int G, int criterion, int32_t *best,
+                                  zhsm_result *best_results, cudaStream_t st);
+cudaError_t corridor_launch(const float *scans, const unsigned char *bad, const short *seg, const float *fi,
+                            const float *si, const float *co, int S, int n, signed char *out, cudaStream_t st);
 zhsm_status zhsm_stage(zhsm_handle *h, int slot, size_t bytes, void **out);
 
 cudaError_t plicp_launch(const PlicpArgs &a, int sm_count, cudaStream_t st, int *launched);

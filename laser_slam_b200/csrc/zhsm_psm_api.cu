@@ -152,6 +152,31 @@ extern "C" zhsm_status zhsm_scan_project_batch(zhsm_handle *h, const float *scan
     return ZHSM_OK;
 }
 
+extern "C" zhsm_status zhsm_is_corridor_batch(zhsm_handle *h, const float *scans, const uint8_t *bad, const int16_t *seg,
+                                              int S, int8_t *out, unsigned flags, void *cuda_stream) {
+    if (!h || !scans || !bad || !seg || !out || S < 0) return ZHSM_ERR_ARG;
+    if (!h->have_laser) { h->err = "zhsm_set_laser not called"; return ZHSM_ERR_ARG; }
+    if (S == 0) return ZHSM_OK;
+    ZHSM_CUDA_TRY(h, cudaSetDevice(h->device));
+    cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : h->stream;
+    const float *ds; const uint8_t *db; const int16_t *dg;
+    zhsm_status s;
+    if ((s = stage_scans(h, scans, bad, seg, S, flags, st, &ds, &db, &dg)) != ZHSM_OK) return s;
+    int8_t *dout = out;
+    if (!(flags & ZHSM_RESULTS_ON_DEVICE)) {
+        void *p;
+        if ((s = zhsm_stage(h, 10, (size_t)S, &p)) != ZHSM_OK) return s;
+        dout = (int8_t *)p;
+    }
+    ZHSM_CUDA_TRY(h, corridor_launch(ds, db, (const short *)dg, h->d_fi, h->d_si, h->d_co, S, h->laser.n, (signed char *)dout, st));
+    h->launches++;
+    if (!(flags & ZHSM_RESULTS_ON_DEVICE)) {
+        ZHSM_CUDA_TRY(h, cudaMemcpyAsync(out, dout, (size_t)S, cudaMemcpyDeviceToHost, st));
+        ZHSM_CUDA_TRY(h, cudaStreamSynchronize(st));
+    }
+    return ZHSM_OK;
+}
+
 __global__ void libm_kernel(int which, const float *x, const float *y, float *out, int N) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= N) return;

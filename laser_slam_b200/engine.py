@@ -68,6 +68,7 @@ assert RESULT_DTYPE.itemsize == 128
 SCANS_ON_DEVICE, JOBS_ON_DEVICE, RESULTS_ON_DEVICE, ALL_ON_DEVICE = 1, 2, 4, 7
 FILTER_SCANS, WRITEBACK_SCANS = 8, 16
 ALGO_PSM, ALGO_PM_ICP, ALGO_PSM_ICP, ALGO_FMATCH = 0, 1, 2, 3
+BEST_GOODNESS, BEST_MEAN_ERROR = 0, 1
 
 _lib = None
 
@@ -109,10 +110,11 @@ def load_library():
     L.zhsm_psm_batch.argtypes = [vp, vp, vp, vp, i32, vp, vp, vp, i32, i32, vp, u32, vp]
     L.zhsm_scan_project_batch.argtypes = [vp, vp, vp, vp, i32, vp, vp, i32, vp, vp]
     L.zhsm_debug_libm.argtypes = [vp, i32, vp, vp, vp, i32]
+    L.zhsm_is_corridor_batch.argtypes = [vp, vp, vp, vp, i32, vp, u32, vp]
     L.zhsm_icp_default_options.argtypes = [C.POINTER(IcpOptions)]
     L.zhsm_icp_default_options.restype = None
     L.zhsm_icp_batch.argtypes = [vp, vp, C.c_longlong, vp, vp, i32, vp, vp, vp, i32, C.POINTER(IcpOptions), vp, u32, vp]
-    L.zhsm_best_of_starts.argtypes = [vp, vp, i32, i32, vp, vp, u32, vp]
+    L.zhsm_best_of_starts.argtypes = [vp, vp, i32, i32, i32, vp, vp, u32, vp]
     _lib = L
     return L
 
@@ -253,6 +255,20 @@ class Engine:
                                           _ptr(init_pose), B, int(algo), _ptr(results), flags, stream), "zhsm_psm_batch")
         return results
 
+    def is_corridor(self, scans, bad, seg, stream=None):
+        """pm_is_corridor per preprocessed scan: int8 [S] = 1 corridor, 0 room, -3 / -2 where the reference throws."""
+        S = int(scans.shape[0])
+        if _is_dev(scans):
+            import torch
+            out = torch.empty(S, dtype=torch.int8, device=scans.device)
+            flags = SCANS_ON_DEVICE | RESULTS_ON_DEVICE
+        else:
+            out = np.zeros(S, np.int8)
+            flags = 0
+        self._check(self.L.zhsm_is_corridor_batch(self.h, _ptr(scans), _ptr(bad), _ptr(seg), S, _ptr(out), flags, stream),
+                    "zhsm_is_corridor_batch")
+        return out
+
     def scan_project(self, scans, bad, seg, idx, pose):
         """pm_scan_project of scans[idx[k]] at pose[k] (host arrays) -> (new_r float32 [B][n], new_bad uint8 [B][n])."""
         idx = np.ascontiguousarray(idx, np.int32)
@@ -295,8 +311,8 @@ class Engine:
                                           _ptr(results), flags, stream), "zhsm_icp_batch")
         return results
 
-    def best_of_starts(self, results, P, G, stream=None):
-        """Per pair the start with the highest goodness: returns (best index [P], best record [P])."""
+    def best_of_starts(self, results, P, G, criterion=BEST_GOODNESS, stream=None):
+        """Per pair the preferred start (see zhsm_best_of_starts): returns (best index [P], best record [P])."""
         if _is_dev(results):
             import torch
             best = torch.empty(P, dtype=torch.int32, device=results.device)
@@ -306,7 +322,7 @@ class Engine:
             best = np.zeros(P, np.int32)
             rec = np.zeros(P, RESULT_DTYPE)
             flags = 0
-        self._check(self.L.zhsm_best_of_starts(self.h, _ptr(results), int(P), int(G), _ptr(best), _ptr(rec), flags,
+        self._check(self.L.zhsm_best_of_starts(self.h, _ptr(results), int(P), int(G), int(criterion), _ptr(best), _ptr(rec), flags,
                                                stream), "zhsm_best_of_starts")
         return best, rec
 

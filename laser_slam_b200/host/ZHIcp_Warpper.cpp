@@ -37,7 +37,7 @@ float CICPWarpper::ICPMatchMultiStart(const float *rx, const float *ry, int N1, 
     int best = 0;
     if (G > 1) {
         int32_t b = -1;
-        check(h_, zhsm_best_of_starts(h_, &res[0], 1, G, &b, 0, 0, 0), "zhsm_best_of_starts");
+        check(h_, zhsm_best_of_starts(h_, &res[0], 1, G, ZHSM_BEST_GOODNESS, &b, 0, 0, 0), "zhsm_best_of_starts");
         best = b < 0 ? 0 : b;
     }
     last = res[best];

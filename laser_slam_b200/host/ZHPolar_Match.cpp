@@ -85,6 +85,15 @@ void CPolarMatch::pm_scan_project(const PMScan *act, float *new_r, int *new_bad)
     for (int i = 0; i < n; i++) new_bad[i] = nb[i];
 }
 
+bool CPolarMatch::pm_is_corridor(PMScan *act) {
+    Packed p(1, m_pParam->pm_l_points);
+    p.put(0, act);
+    int8_t out = 0;
+    check(h_, zhsm_is_corridor_batch(h_, &p.r[0], &p.bad[0], &p.seg[0], 1, &out, 0, 0), "zhsm_is_corridor_batch");
+    if (out < 0) throw (int)(-out);
+    return out == 1;
+}
+
 // pm_psm / pm_icp move the current scan into the reference scan's frame first (:918-925, PM_LASER_Y = 0), in float
 // with the host's sinf/cosf exactly as the reference does; the kernel then works with the ref scan at the origin.
 float CPolarMatch::match(int algo, const PMScan *lsr, PMScan *lsa) {

@@ -13,6 +13,7 @@
 //   FMatch(lsr, lsa, bFirst)     preprocess (lsr too when bFirst), zero both poses, pm_icp, pm_error_index2;
 //                                (-1,-1) on failure (:81-121)
 //   pm_scan_project(act, new_r, new_bad)   (:1356-1479)
+//   pm_is_corridor(act)          (:2058-2186)
 // and FMatchBatch(): many independent pairs in one launch.
 // There is no CPU path: construction throws std::runtime_error when no sm_100 GPU / libzhsm.so is usable.
 #ifndef ZHSM_HOST_ZHPOLAR_MATCH_H
@@ -33,6 +34,7 @@ public:
     void pm_preprocessScan(PMScan *ls);
     void pm_median_filter(PMScan *ls);
     void pm_scan_project(const PMScan *act, float *new_r, int *new_bad);
+    bool pm_is_corridor(PMScan *act);  // throws 3 / 2 like the reference when fewer than two line directions exist
     float pm_psm(const PMScan *lsr, PMScan *lsa);
     float pm_icp(const PMScan *lsr, PMScan *lsa);
     // pairs (refs[k], acts[k]); preprocesses acts (and refs when preprocess_refs); out[k] = FMatch's return value

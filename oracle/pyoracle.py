@@ -215,6 +215,11 @@ class RefPolarMatch:
         ref().zhpsm_ref_median(self.h, r.ctypes.data)
         return r
 
+    def is_corridor(self, r, bad, seg):
+        """pm_is_corridor on a preprocessed scan: 1 / 0, or -3 / -2 when the reference throws 3 / 2."""
+        r, bad, seg = _f32(r), _i32(bad), _i32(seg)
+        return int(ref().zhpsm_ref_is_corridor(self.h, r.ctypes.data, bad.ctypes.data, seg.ctypes.data))
+
     def scan_project(self, r, bad, seg, pose):
         r, bad, seg = _f32(r), _i32(bad), _i32(seg)
         pose = np.asarray(pose, np.float32)

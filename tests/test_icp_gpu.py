@@ -77,10 +77,16 @@ def test_against_live_oracle_multistart(eng, nodes):
     o = po.mrpt_icp_batch(d["pts"], d["off"], d["cnt"], ri, ci, init, nthreads=os.cpu_count() or 4)
     r = eng.icp(d["pts"], d["off"], d["cnt"], ri, ci, init)
     _compare(r, o, pose_frac=0.97, iter_frac=0.97)
-    # best-of-G on the device == the host rule (highest goodness, lowest index on ties)
+    # best-of-G on the device == the host rule (highest goodness, then lowest error, then lowest index)
     best, rec = eng.best_of_starts(r, P, G)
-    g = np.where(r["valid"] != 0, r["goodness"], -np.inf).reshape(P, G)
-    assert np.array_equal(best, g.argmax(1).astype(np.int32))
+    rr = r.reshape(P, G)
+    want = np.array([min((g for g in range(G) if rr[p, g]["valid"]), default=-1,
+                         key=lambda g: (-float(rr[p, g]["goodness"]), float(rr[p, g]["error"]), g)) for p in range(P)], np.int32)
+    assert np.array_equal(best, want)
+    # PL-ICP criterion on the same records: lowest error / nvalid
+    best2, _ = eng.best_of_starts(r, P, G, criterion=1)
+    score = np.where(rr["valid"] != 0, rr["error"] / np.maximum(rr["nvalid"], 1), np.inf)
+    assert np.array_equal(best2, score.argmin(1).astype(np.int32))
     assert np.array_equal(rec["x"], r["x"].reshape(P, G, 3)[np.arange(P), best])
     del rng
 

@@ -110,3 +110,21 @@ def test_fmatch_error_index(engine, pre, log):
     rel = np.abs(got - want) / np.maximum(np.abs(want), 1e-12)
     print(f"\n{log}: pm_error_index2 identical={(got == want)[ok].all(1).mean():.5f} max rel={rel[ok].max():.3g}")
     assert (rel[ok].max(1) < 1e-3).mean() >= 0.999
+
+
+def test_is_corridor(engine, pre):
+    """pm_is_corridor (8a-16) per scan == the reference's own answers (tests/golden/corridor.npz, made by executing
+    the reference): every scan of the three logs, plus synthetic corridors / rooms / nearly empty scans that reach the
+    corridor branch and the `throw 3` path."""
+    import os
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "corridor.npz"))
+    for log in LOGS:
+        g, r, bad, seg = pre(log)
+        got = engine.is_corridor(r, bad, seg)
+        assert np.array_equal(got, z[log]), (log, np.nonzero(got != z[log])[0][:10])
+    lz = E.laser_from_table("LMS511")
+    engine.set_laser(lz)
+    r, bad, seg = engine.preprocess(z["synth_scans"].astype(np.float32))
+    got = engine.is_corridor(r, bad, seg)
+    assert np.array_equal(got, z["synth_flags"]), np.nonzero(got != z["synth_flags"])[0]
+    assert set(np.unique(got)) == {-3, 0, 1}
