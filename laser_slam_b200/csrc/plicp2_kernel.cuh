@@ -30,13 +30,15 @@ __device__ __forceinline__ bool search_ray(const Lay &l, const WalkCtx &w, const
 // sens: bit k = ray k*T+t exists and is valid; returns the mask of rays holding a correspondence.
 template <int T>
 __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const WalkCtx &w, const IterCtx &it, int C,
-                                                         unsigned sens) {
+                                                         unsigned sens, int &nsearch, int &nround) {
     const int t = threadIdx.x;
     unsigned valid = 0;
 #pragma unroll 1
     for (int k = 0; k < C; k++)
-        if (sens >> k & 1u)
+        if (sens >> k & 1u) {
+            nsearch += 0x10001;
             if (search_ray(l, w, it, k * T + t)) valid |= 1u << k;
+        }
     __syncthreads();
     const short *cj1 = PL_SH(const short, l.cj1);
     short *spec = PL_SH(short, l.spec);
@@ -55,11 +57,14 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
         }
         if (!__syncthreads_or((int)need)) break;
 #pragma unroll 1
-        for (int k = 0; k < C; k++)
+        for (int k = 0; k < C; k++) {
+            nround += __any_sync(0xffffffffu, need >> k & 1u) ? 1 : 0;  // diagnostics: warp rounds of re-searches
             if (need >> k & 1u) {
+                nsearch += 1;
                 if (search_ray(l, w, it, k * T + t)) valid |= 1u << k;
                 else valid &= ~(1u << k);
             }
+        }
         __syncthreads();
     }
     return valid;
@@ -145,6 +150,7 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
     double best_x[3] = {0, 0, 0}, x_first[3] = {0, 0, 0}, best_error = 0;
     int iterations = 0, nvalid0 = 0, n_loops = 0, restarted = 0, valid_out = 0, status = ZHSM_JOB_OK;
     unsigned valid = 0;
+    int nsearch = 0, nround = 0;  // diagnostics: low 16 bits walks by this thread, high 16 first-pass walks; warp rounds
 
     for (int loop = 0; loop < 7; loop++) {
         int iteration = 0, all_ok = 1, par = 0, newest = 0;
@@ -155,7 +161,7 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
             it.sn = ctl->sn[par];
             for (int j = t; j < n; j += T) d2j[j] = BIG;
             if (t == 0) ctl->hash_acc[iteration & 1] = 0;
-            valid = find_correspondences<T>(l, wc, it, C, sens);
+            valid = find_correspondences<T>(l, wc, it, C, sens, nsearch, nround);
             // kill_outliers_double (icp_outliers.c): min dist2_j1 per ref index.  dist2_j1 is recomputed
             // from the same operands the walk used (bit-identical), so it needs no storage.
             if (P.outliers_remove_doubles) {
@@ -376,7 +382,7 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
         it.cs = ctl->cs[0];
         it.sn = ctl->sn[0];
         // "recompute correspondences in case of restarts" (icp.c): world coords at best x + tricks, no outlier pass
-        if (v_restarted) valid = find_correspondences<T>(l, wc, it, C, sens);
+        if (v_restarted) valid = find_correspondences<T>(l, wc, it, C, sens, nsearch, nround);
     }
     if (t == 0) ctl->hash_acc[0] = 0;
 #pragma unroll 1
@@ -394,6 +400,9 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
         if (lane == 0 && hc) atomicXor(&ctl->hash_acc[0], hc);
     }
     __syncthreads();
+    const int walks_all = block_sum<T>(nsearch & 0xffff, ctl->ired, 0);
+    const int rewalk_rounds = block_sum<T>(lane == 0 ? nround : 0, ctl->ired, 2);
+    const int walks_first = block_sum<T>(nsearch >> 16, ctl->ired, 1);
     double cov[6] = {0, 0, 0, 0, 0, 0};
     if (v_ok && P.do_compute_covariance)
         covariance_exact<T>(l, n, C, a.cs, it.x0, it.x1, it.cs, it.sn, P.sigma, cov);
@@ -403,6 +412,9 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
         r.status = valid_out ? ZHSM_JOB_OK : status;
         r.iterations = iterations;
         r.n_loops = n_loops;
+        r.reserved[0] = walks_all;    // diagnostics: ray walks executed (speculation + re-searches)
+        r.reserved[1] = walks_first;
+        r.reserved[2] = rewalk_rounds;  // ... warp-level rounds spent on re-searches  // ... of which first-pass walks (= what the sequential algorithm does)
         if (valid_out) {
             r.x[0] = best_x[0];
             r.x[1] = best_x[1];
