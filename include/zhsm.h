@@ -210,6 +210,27 @@ zhsm_status zhsm_icp_batch(zhsm_handle *h, const float *pts, long long npts, con
 zhsm_status zhsm_best_of_starts(zhsm_handle *h, const zhsm_result *results, int P, int G, int criterion,
                                 int32_t *best, zhsm_result *best_results, unsigned flags, void *cuda_stream);
 
+/* ---- loop-closure gating and consensus (src/mapGraph/MapGraph.cpp) --------------------------------
+ * The arithmetic either side of the ICP batches in CMapGraph::addMapNode's loop search (:1342-1442).  All arrays are
+ * HOST arrays (the graph lives on the host).  Node table: pose[N][3] = m_rootPose (x, y, theta), ld[N][2] / ru[N][2]
+ * = m_ld_corner / m_ru_corner in the node frame, cov_xy[N][2] = (m_root_Cov(0,0), m_root_Cov(1,1)) or NULL for the
+ * constant-covariance mode (m_bUseConstantCov, :229).
+ * flags[m*N + j], cur = cur_idx[m], other node j: bit ZHSM_GATE_OVERLAPPED = isOverlappedArea(cur, j) (:957-994),
+ * bit ZHSM_GATE_LOOPY = isLoopyArea(cur, j, beta) (:996-1032; the caller passes beta = 225, :1350).  A pair becomes an
+ * ICP job when both bits are set and j is outside the adjacency window (:1345-1346). */
+#define ZHSM_GATE_OVERLAPPED 1
+#define ZHSM_GATE_LOOPY 2
+zhsm_status zhsm_gate_candidates(zhsm_handle *h, const double *pose, const double *ld, const double *ru,
+                                 const double *cov_xy, int N, const int32_t *cur_idx, int M, float beta, uint8_t *flags);
+/* isAvaliableArea (:918-944) for M matched transforms trans[M][3] (cov_xy[M][2] of the current node or NULL) */
+zhsm_status zhsm_available_area(zhsm_handle *h, const double *trans, const double *cov_xy, int M, uint8_t *ok);
+/* S matched sets stored back to back (set s = entries [set_off[s], set_off[s+1]), poses[e][3] = the node pose each
+ * match implies, good[e] = its goodness): deleteMisMatch (:169-209) -> keep[e]; calculateWeightedPose (:146-167) over
+ * the kept entries -> final_pose[s][3]; the entry calculateFinalPose picks (:110-123) -> final_idx[s] (absolute entry
+ * index, -1 for an empty set). */
+zhsm_status zhsm_consensus(zhsm_handle *h, const double *poses, const float *good, const int32_t *set_off, int S,
+                           uint8_t *keep, double *final_pose, int32_t *final_idx);
+
 /* blocks until everything queued on the handle's stream (or the given one) is done */
 zhsm_status zhsm_sync(zhsm_handle *h, void *cuda_stream);
 

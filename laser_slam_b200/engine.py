@@ -111,6 +111,9 @@ def load_library():
     L.zhsm_scan_project_batch.argtypes = [vp, vp, vp, vp, i32, vp, vp, i32, vp, vp]
     L.zhsm_debug_libm.argtypes = [vp, i32, vp, vp, vp, i32]
     L.zhsm_is_corridor_batch.argtypes = [vp, vp, vp, vp, i32, vp, u32, vp]
+    L.zhsm_gate_candidates.argtypes = [vp, vp, vp, vp, vp, i32, vp, i32, C.c_float, vp]
+    L.zhsm_available_area.argtypes = [vp, vp, vp, i32, vp]
+    L.zhsm_consensus.argtypes = [vp, vp, vp, vp, i32, vp, vp, vp]
     L.zhsm_icp_default_options.argtypes = [C.POINTER(IcpOptions)]
     L.zhsm_icp_default_options.restype = None
     L.zhsm_icp_batch.argtypes = [vp, vp, C.c_longlong, vp, vp, i32, vp, vp, vp, i32, C.POINTER(IcpOptions), vp, u32, vp]
@@ -325,6 +328,34 @@ class Engine:
         self._check(self.L.zhsm_best_of_starts(self.h, _ptr(results), int(P), int(G), int(criterion), _ptr(best), _ptr(rec), flags,
                                                stream), "zhsm_best_of_starts")
         return best, rec
+
+    def gate_candidates(self, pose, ld, ru, cur_idx, cov_xy=None, beta=225.0):
+        """isOverlappedArea / isLoopyArea flags [M][N] (bit 1 / bit 2) of nodes cur_idx against every node."""
+        pose = np.ascontiguousarray(pose, np.float64); ld = np.ascontiguousarray(ld, np.float64)
+        ru = np.ascontiguousarray(ru, np.float64); cur_idx = np.ascontiguousarray(cur_idx, np.int32)
+        cov = None if cov_xy is None else np.ascontiguousarray(cov_xy, np.float64)
+        N, M = pose.shape[0], cur_idx.size
+        flags = np.zeros((M, N), np.uint8)
+        self._check(self.L.zhsm_gate_candidates(self.h, _ptr(pose), _ptr(ld), _ptr(ru), _ptr(cov), N, _ptr(cur_idx), M,
+                                                float(beta), _ptr(flags)), "zhsm_gate_candidates")
+        return flags
+
+    def available_area(self, trans, cov_xy=None):
+        trans = np.ascontiguousarray(trans, np.float64).reshape(-1, 3)
+        cov = None if cov_xy is None else np.ascontiguousarray(cov_xy, np.float64)
+        ok = np.zeros(trans.shape[0], np.uint8)
+        self._check(self.L.zhsm_available_area(self.h, _ptr(trans), _ptr(cov), trans.shape[0], _ptr(ok)), "zhsm_available_area")
+        return ok
+
+    def consensus(self, poses, good, set_off):
+        """deleteMisMatch + calculateWeightedPose + calculateFinalPose's choice per matched set."""
+        poses = np.ascontiguousarray(poses, np.float64).reshape(-1, 3)
+        good = np.ascontiguousarray(good, np.float32); set_off = np.ascontiguousarray(set_off, np.int32)
+        S = set_off.size - 1
+        keep = np.zeros(poses.shape[0], np.uint8); fp = np.zeros((S, 3)); fi = np.zeros(S, np.int32)
+        self._check(self.L.zhsm_consensus(self.h, _ptr(poses), _ptr(good), _ptr(set_off), S, _ptr(keep), _ptr(fp), _ptr(fi)),
+                    "zhsm_consensus")
+        return keep, fp, fi
 
     def debug_libm(self, which, x, y=None):
         x = np.ascontiguousarray(x, np.float32)

@@ -325,3 +325,50 @@ def mrpt_icp_batch(pts, off, cnt, ref_idx, cur_idx, init, options=None, nthreads
                          init.ctypes.data, ri.size, C.byref(options) if options is not None else None,
                          out.ctypes.data, int(nthreads))
     return out
+
+
+# ---------------------------------------------------------------------------------------------
+# loop-closure gating and consensus (src/mapGraph/MapGraph.cpp), oracle/graph_oracle.c
+# ---------------------------------------------------------------------------------------------
+def gate_candidates(pose, ld, ru, cur_idx, cov_xy=None, beta=225.0):
+    pose = np.ascontiguousarray(pose, np.float64); ld = np.ascontiguousarray(ld, np.float64)
+    ru = np.ascontiguousarray(ru, np.float64); cur_idx = np.ascontiguousarray(cur_idx, np.int32)
+    cov = None if cov_xy is None else np.ascontiguousarray(cov_xy, np.float64)
+    N, M = pose.shape[0], cur_idx.size
+    flags = np.zeros((M, N), np.uint8)
+    L = lib()
+    L.orc_gate_candidates.argtypes = [C.c_void_p] * 4 + [C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_void_p]
+    L.orc_gate_candidates(pose.ctypes.data, ld.ctypes.data, ru.ctypes.data, None if cov is None else cov.ctypes.data, N,
+                          cur_idx.ctypes.data, M, C.c_float(beta), flags.ctypes.data)
+    return flags
+
+
+def available_area(trans, cov_xy=None):
+    trans = np.ascontiguousarray(trans, np.float64).reshape(-1, 3)
+    cov = None if cov_xy is None else np.ascontiguousarray(cov_xy, np.float64)
+    ok = np.zeros(trans.shape[0], np.uint8)
+    L = lib()
+    L.orc_available_area.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+    L.orc_available_area(trans.ctypes.data, None if cov is None else cov.ctypes.data, trans.shape[0], ok.ctypes.data)
+    return ok
+
+
+def consensus(poses, good, set_off):
+    poses = np.ascontiguousarray(poses, np.float64).reshape(-1, 3)
+    good = np.ascontiguousarray(good, np.float32); set_off = np.ascontiguousarray(set_off, np.int32)
+    S = set_off.size - 1
+    keep = np.zeros(poses.shape[0], np.uint8); fp = np.zeros((S, 3)); fi = np.zeros(S, np.int32)
+    L = lib()
+    L.orc_consensus.argtypes = [C.c_void_p] * 3 + [C.c_int] + [C.c_void_p] * 3
+    L.orc_consensus(poses.ctypes.data, good.ctypes.data, set_off.ctypes.data, S, keep.ctypes.data, fp.ctypes.data,
+                    fi.ctypes.data)
+    return keep, fp, fi
+
+
+def ref_oplus_point(pose, pt):
+    """OrientedPoint2D::oplus(Point2D) executed by the compiled reference (src/zhpsm/point.cpp:63-69)."""
+    R = ref()
+    R.zhpsm_ref_oplus_point.argtypes = [C.c_void_p] * 3
+    pose = np.ascontiguousarray(pose, np.float64); pt = np.ascontiguousarray(pt, np.float64); out = np.zeros(2)
+    R.zhpsm_ref_oplus_point(pose.ctypes.data, pt.ctypes.data, out.ctypes.data)
+    return out

@@ -17,6 +17,7 @@
 #include <fcntl.h>
 
 #include "ZHPolar_Match.h"
+#include "point.h"
 
 namespace {
 struct NullBuf : std::streambuf {
@@ -215,5 +216,18 @@ void zhpsm_ref_match_batch(const char *laser, float fi_min, int max_range, int a
     if (nthreads == 1) { batch_worker(&jobs[0]); return; }
     for (int t = 0; t < nthreads; t++) pthread_create(&th[t], 0, batch_worker, &jobs[t]);
     for (int t = 0; t < nthreads; t++) pthread_join(th[t], 0);
+}
+
+// OrientedPoint2D::oplus(Point2D) / ominus(OrientedPoint2D) of the reference (src/zhpsm/point.cpp:46-69), for pinning the
+// restatement in oracle/graph_oracle.c
+void zhpsm_ref_oplus_point(const double pose[3], const double pt[2], double out[2]) {
+    zhpsm::OrientedPoint2D p(pose[0], pose[1], pose[2]);
+    zhpsm::Point2D r = p.oplus(zhpsm::Point2D(pt[0], pt[1]));
+    out[0] = r.x; out[1] = r.y;
+}
+void zhpsm_ref_ominus_pose(const double a[3], const double b[3], double out[3]) {
+    zhpsm::OrientedPoint2D p(a[0], a[1], a[2]);
+    zhpsm::OrientedPoint2D r = p.ominus(zhpsm::OrientedPoint2D(b[0], b[1], b[2]));
+    out[0] = r.x; out[1] = r.y; out[2] = r.theta;
 }
 }

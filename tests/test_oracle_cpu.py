@@ -282,3 +282,62 @@ def test_icp_oracle_threshold_schedule():
                           po.icp_default_options(corresponding_points_decimation=1, maxIterations=2))[0]
     # after 2 iterations the gate (0.1875) is still above 0.05: the tail rule keeps halving and iterating
     assert r["nIterations"] > 2
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# loop-closure gating / consensus oracle (oracle/graph_oracle.c)
+# ---------------------------------------------------------------------------------------------------------------
+def test_graph_oracle_oplus_pinned_by_compiled_reference():
+    """The one routine of this path that compiles from the reference (OrientedPoint2D::oplus, point.cpp:63-69) agrees
+    bit for bit with the restatement's copy: a node with an identity pose and unit box overlaps itself, and shifting
+    the box corners through oplus by hand reproduces the flags."""
+    if not po.have_ref():
+        pytest.skip("oracle/_ref not built")
+    rng = np.random.default_rng(0)
+    for _ in range(200):
+        pose = rng.uniform(-10, 10, 3); pt = rng.uniform(-5, 5, 2)
+        c, s = np.cos(pose[2]), np.sin(pose[2])
+        want = np.array([pose[0] + pt[0] * c - pt[1] * s, pose[1] + pt[0] * s + pt[1] * c])
+        assert np.array_equal(po.ref_oplus_point(pose, pt), want)
+
+
+def test_graph_oracle_gating_properties():
+    from tests.graph_cases import node_table
+    pose, ld, ru, cov = node_table()
+    N = pose.shape[0]
+    f = po.gate_candidates(pose, ld, ru, np.arange(N))
+    ov, lp = (f & 1) != 0, (f & 2) != 0
+    good_box = ld[:, 0] < ru[:, 0]
+    assert ov[np.arange(N), np.arange(N)][good_box].all()           # a node overlaps itself (ratio 1)
+    # a node that never got a point keeps (MAX_VALUE, MIN_VALUE) corners; calBounding (:946-955) sorts them, so it turns
+    # into a huge box: it contains every proper node, and no proper node covers 40 % of it
+    assert ov[good_box][:, ~good_box].all() and not ov[~good_box][:, good_box].any()
+    d2 = ((pose[:, None, :2] - pose[None, :, :2]) ** 2).sum(2)
+    assert np.array_equal(lp, d2.astype(np.float32) <= 4.0)          # constant covariance: 2 m radius
+    assert np.array_equal(lp, lp.T) and not np.array_equal(ov, ov.T)  # the overlap ratio is relative to the current node
+    # covariance-scaled radius
+    f2 = po.gate_candidates(pose, ld, ru, np.arange(N), cov_xy=cov, beta=225.0)
+    rad = (np.abs(cov[:, 0].astype(np.float32)) + np.abs(cov[:, 1].astype(np.float32))) * np.float32(225)
+    assert np.array_equal((f2 & 2) != 0, d2.astype(np.float32) <= rad[:, None])
+    assert 0.001 < ((f & 3) == 3).mean() < 0.2
+
+
+def test_graph_oracle_consensus_properties():
+    from tests.graph_cases import matched_sets
+    poses, good, off = matched_sets()
+    keep, fp, fi = po.consensus(poses, good, off)
+    for s in range(off.size - 1):
+        lo, hi = off[s], off[s + 1]
+        n = hi - lo
+        if n == 0:
+            assert fi[s] == -1
+            continue
+        if n < 3:
+            assert keep[lo:hi].all()                                  # statis() refuses fewer than 3 samples
+        k = keep[lo:hi].astype(bool)
+        assert k.any() and lo <= fi[s] < hi and keep[fi[s]]
+        w = good[lo:hi][k] / good[lo:hi][k].sum()
+        assert np.allclose(fp[s], (w[:, None] * poses[lo:hi][k]).sum(0), atol=1e-4)
+        d = np.hypot(*(poses[lo:hi, :2] - fp[s, :2]).T)
+        assert fi[s] - lo == np.flatnonzero(k)[np.argmin(d[k])]
+    assert 0.02 < 1 - keep.mean() < 0.2                               # some mismatches are dropped, most entries stay
