@@ -231,6 +231,14 @@ zhsm_status zhsm_available_area(zhsm_handle *h, const double *trans, const doubl
 zhsm_status zhsm_consensus(zhsm_handle *h, const double *poses, const float *good, const int32_t *set_off, int S,
                            uint8_t *keep, double *final_pose, int32_t *final_idx);
 
+/* ---- submap cloud builder (src/mapGraph/MapNode.cpp:726-757 computePMAP + src/mapGraph/PMap.cpp) -------
+ * Builds the point cloud zhicp aligns: K scans (scans[K][n] float cm, the handle's laser geometry) taken at traj[K][3]
+ * (x, y, theta in the node frame, doubles like m_trajectory) are traced through a 5 cm hit/visit grid and the cells
+ * whose hit ratio is exactly 1 are returned as (x, y) in metres, in the reference's row-major cell order.
+ * *count = number of cloud points (may exceed cap; only cap are written); dims (optional) = grid size.  Host arrays. */
+zhsm_status zhsm_submap_cloud(zhsm_handle *h, const float *scans, const double *traj, int K, float *out_x, float *out_y,
+                              int cap, int *count, int *dims);
+
 /* blocks until everything queued on the handle's stream (or the given one) is done */
 zhsm_status zhsm_sync(zhsm_handle *h, void *cuda_stream);
 

@@ -114,6 +114,7 @@ def load_library():
     L.zhsm_gate_candidates.argtypes = [vp, vp, vp, vp, vp, i32, vp, i32, C.c_float, vp]
     L.zhsm_available_area.argtypes = [vp, vp, vp, i32, vp]
     L.zhsm_consensus.argtypes = [vp, vp, vp, vp, i32, vp, vp, vp]
+    L.zhsm_submap_cloud.argtypes = [vp, vp, vp, i32, vp, vp, i32, vp, vp]
     L.zhsm_icp_default_options.argtypes = [C.POINTER(IcpOptions)]
     L.zhsm_icp_default_options.restype = None
     L.zhsm_icp_batch.argtypes = [vp, vp, C.c_longlong, vp, vp, i32, vp, vp, vp, i32, C.POINTER(IcpOptions), vp, u32, vp]
@@ -356,6 +357,17 @@ class Engine:
         self._check(self.L.zhsm_consensus(self.h, _ptr(poses), _ptr(good), _ptr(set_off), S, _ptr(keep), _ptr(fp), _ptr(fi)),
                     "zhsm_consensus")
         return keep, fp, fi
+
+    def submap_cloud(self, scans_cm, traj, cap=1 << 20):
+        """CMapNode::computePMAP: occupied 5 cm cells of K scans taken at traj [K][3]; returns (x, y, grid dims)."""
+        scans = np.ascontiguousarray(scans_cm, np.float32); traj = np.ascontiguousarray(traj, np.float64)
+        x = np.zeros(cap, np.float32); y = np.zeros(cap, np.float32)
+        cnt = C.c_int(0); dims = np.zeros(2, np.int32)
+        self._check(self.L.zhsm_submap_cloud(self.h, _ptr(scans), _ptr(traj), scans.shape[0], _ptr(x), _ptr(y), cap,
+                                             C.byref(cnt), _ptr(dims)), "zhsm_submap_cloud")
+        if cnt.value > cap:
+            raise ZhsmError(f"submap cloud has {cnt.value} points, capacity {cap}")
+        return x[:cnt.value].copy(), y[:cnt.value].copy(), dims
 
     def debug_libm(self, which, x, y=None):
         x = np.ascontiguousarray(x, np.float32)

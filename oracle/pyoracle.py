@@ -372,3 +372,35 @@ def ref_oplus_point(pose, pt):
     pose = np.ascontiguousarray(pose, np.float64); pt = np.ascontiguousarray(pt, np.float64); out = np.zeros(2)
     R.zhpsm_ref_oplus_point(pose.ctypes.data, pt.ctypes.data, out.ctypes.data)
     return out
+
+
+# ---------------------------------------------------------------------------------------------
+# submap cloud builder: the reference's own CPMap (src/mapGraph/PMap.cpp, line.cpp) compiled into oracle/_ref
+# ---------------------------------------------------------------------------------------------
+_PMAP = os.path.join(_HERE, "_ref", "libpmap_ref.so")
+_pmap = None
+
+
+def have_pmap_ref():
+    return os.path.exists(_PMAP)
+
+
+def ref_submap_cloud(scans_cm, traj, min_angle, dfi, max_range_cm, cap=1 << 20):
+    """CMapNode::computePMAP (src/mapGraph/MapNode.cpp:726-757) on K scans [K][n] (cm) taken at traj [K][3]:
+    returns (x, y) float32 of the occupied cells, in the reference's row-major cell order, and the grid size."""
+    global _pmap
+    if _pmap is None:
+        if not os.path.exists(_PMAP):
+            raise RuntimeError("oracle/_ref/libpmap_ref.so is absent (make -C oracle ref, where /root/reference exists)")
+        _pmap = C.CDLL(_PMAP)
+        _pmap.pmap_ref_submap_cloud.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_int,
+                                                C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        _pmap.pmap_ref_submap_cloud.restype = C.c_int
+    scans = np.ascontiguousarray(scans_cm, np.float32)
+    traj = np.ascontiguousarray(traj, np.float64)
+    x = np.zeros(cap, np.float32); y = np.zeros(cap, np.float32); dims = np.zeros(2, np.int32)
+    cnt = _pmap.pmap_ref_submap_cloud(scans.ctypes.data, traj.ctypes.data, scans.shape[0], scans.shape[1],
+                                      C.c_float(min_angle), C.c_float(dfi), int(max_range_cm), x.ctypes.data,
+                                      y.ctypes.data, cap, dims.ctypes.data)
+    assert cnt <= cap
+    return x[:cnt].copy(), y[:cnt].copy(), dims
