@@ -63,7 +63,7 @@ def build_host(verbose=False):
     root = os.path.dirname(HERE)
     host = os.path.join(HERE, "host")
     out = os.path.join(HERE, "libzhsm_host.so")
-    srcs = [os.path.join(host, f) for f in ("ZHCanonical_Matcher.cpp", "ZHPolar_Match.cpp", "ZHIcp_Warpper.cpp")]
+    srcs = [os.path.join(host, f) for f in ("ZHCanonical_Matcher.cpp", "ZHPolar_Match.cpp", "ZHIcp_Warpper.cpp", "zh_carmen.cpp")]
     deps = srcs + [os.path.join(host, f) for f in os.listdir(host) if f.endswith(".h")] + [os.path.join(root, "include", "zhsm.h")]
     cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
     if not os.path.exists(out) or os.path.getmtime(out) < newest(deps):

@@ -39,7 +39,28 @@ void CPolarMatch::pm_init() {
     check(h_, zhsm_set_laser(h_, &lz), "zhsm_set_laser");
 }
 
+void CPolarMatch::clearRecord() {
+    for (size_t i = 0; i < m_SickScans.size(); i++) delete m_SickScans[i];
+    m_SickScans.clear();
+}
+
+bool CPolarMatch::readCarmon(std::string filename, std::string laser) {
+    if (!m_bReady) { printf("Laser is not right initialized!\n"); return false; }
+    clearRecord();
+    ZhCarmenLog log;
+    if (!zh_read_carmen(filename, laser, m_pParam, &log)) return false;
+    pm_init();  // the header may have changed pm_fi_min / pm_max_range (:227-235)
+    for (int k = 0; k < log.S; k++) {
+        PMScan *ls = new PMScan(log.n);
+        memcpy(ls->r, &log.r[(size_t)k * log.n], sizeof(float) * log.n);
+        ls->rx = (float)log.pose[3 * k]; ls->ry = (float)log.pose[3 * k + 1]; ls->th = (float)log.pose[3 * k + 2];
+        m_SickScans.push_back(ls);
+    }
+    return !m_SickScans.empty();
+}
+
 CPolarMatch::~CPolarMatch() {
+    clearRecord();
     zhsm_destroy(h_);
     delete m_pParam;
 }

@@ -24,6 +24,7 @@
 
 #include "../../include/zhsm.h"
 #include "zh_scan.h"
+#include "zh_carmen.h"
 
 class CPolarMatch {
 public:
@@ -40,8 +41,14 @@ public:
     // pairs (refs[k], acts[k]); preprocesses acts (and refs when preprocess_refs); out[k] = FMatch's return value
     void FMatchBatch(PMScan **refs, PMScan **acts, int B, bool preprocess_refs, std::pair<float, float> *out);
 
+    // log input (:172-289): fills m_SickScans and overrides the geometry from the log header, then pm_init()
+    bool readCarmon(std::string filename, std::string laser = "");
+    bool readFlirt(std::string filename) { return readCarmon(filename, "ROBOTLASER1"); }
+    void clearRecord();
+
     Base_PARAM *m_pParam;
     bool m_bReady;
+    std::vector<PMScan *> m_SickScans;
 
 private:
     zhsm_handle *h_;

@@ -230,4 +230,22 @@ void zhpsm_ref_ominus_pose(const double a[3], const double b[3], double out[3]) 
     zhpsm::OrientedPoint2D r = p.ominus(zhpsm::OrientedPoint2D(b[0], b[1], b[2]));
     out[0] = r.x; out[1] = r.y; out[2] = r.theta;
 }
+
+// CPolarMatch::readCarmon (ZHPolar_Match.cpp:172-284) executed by the reference: scans [cap][n] float cm, poses [cap][3],
+// geometry after the header override (fi_min, max_range).  Returns the number of scans read (-1 on failure).
+int zhpsm_ref_read_carmen(const char *laser_name, const char *file, const char *tag, float *scans, float *poses, int cap,
+                          float *fi_min, int *max_range) {
+    silence();
+    CPolarMatch m(laser_name);
+    if (!m.m_bReady) return -1;
+    if (!m.readCarmon(file, tag)) return -1;
+    const int n = m.m_pParam->pm_l_points, S = (int)m.m_SickScans.size();
+    for (int k = 0; k < S && k < cap; k++) {
+        memcpy(scans + (size_t)k * n, m.m_SickScans[k]->r, sizeof(float) * n);
+        poses[3 * k] = m.m_SickScans[k]->rx; poses[3 * k + 1] = m.m_SickScans[k]->ry; poses[3 * k + 2] = m.m_SickScans[k]->th;
+    }
+    *fi_min = m.m_pParam->pm_fi_min;
+    *max_range = m.m_pParam->pm_max_range;
+    return S;
+}
 }
