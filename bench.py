@@ -175,6 +175,46 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def other_paths(zh, eng, dev):
+    """Kernel-only rates (CUDA events inside the library) of the other two matchers on the committed fixtures:
+    zhpsm on fr079 (BASELINE config 2) replicated 8x, zhicp on the reference's node clouds x 64 guesses (config 3)."""
+    import torch
+    from laser_slam_b200 import engine as E
+    sys.path.insert(0, ROOT)
+    from tests.support import load_log, make_laser as fixture_laser
+    out = {}
+    g = load_log("fr079")
+    eng.set_laser(fixture_laser(g))
+    scans = torch.from_numpy(g["scans"].copy()).to(dev)
+    S, n = scans.shape
+    _, bad, seg = eng.preprocess(scans)
+    ri = torch.arange(0, S - 1, dtype=torch.int32, device=dev).repeat(8)
+    ai = ri + 1
+    res = torch.zeros((ri.shape[0], 128), dtype=torch.uint8, device=dev)
+    for name, algo in (("pm_psm", E.ALGO_PSM), ("pm_icp", E.ALGO_PM_ICP)):
+        for _ in range(2):
+            eng.psm(scans, bad, seg, ri, ai, algo=algo, results=res)
+            eng.sync()
+        out[name] = {"jobs_per_s": ri.shape[0] / (eng.last_kernel_ms() * 1e-3), "jobs": int(ri.shape[0]), "beams": int(n),
+                     "workload": "fr079 consecutive pairs x 8"}
+    d = np.load(os.path.join(ROOT, "tests", "golden", "zhicp_nodes.npz"))
+    G, rep = 64, 4
+    gx, gy, gt = np.meshgrid(np.linspace(-0.3, 0.3, 4), np.linspace(-0.3, 0.3, 4), np.linspace(-0.15, 0.15, 4), indexing="ij")
+    grid = np.stack([gx.ravel(), gy.ravel(), gt.ravel()], 1)
+    init = np.tile((d["init"][:, None, :] + grid[None]).reshape(-1, 3), (rep, 1))
+    cri = np.tile(np.repeat(d["pairs"][:, 0], G), rep).astype(np.int32)
+    cci = np.tile(np.repeat(d["pairs"][:, 1], G), rep).astype(np.int32)
+    pts = torch.from_numpy(d["pts"]).to(dev)
+    dri, dci, dinit = torch.from_numpy(cri).to(dev), torch.from_numpy(cci).to(dev), torch.from_numpy(init).to(dev)
+    res = torch.zeros((cri.size, 128), dtype=torch.uint8, device=dev)
+    for _ in range(2):
+        eng.icp(pts, d["off"], d["cnt"], dri, dci, dinit, results=res)
+        eng.sync()
+    out["zhicp"] = {"jobs_per_s": cri.size / (eng.last_kernel_ms() * 1e-3), "jobs": int(cri.size),
+                    "workload": "63 node-cloud pairs of src/zhicp/data{,2} x 64 initial guesses x 4"}
+    return out
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -339,6 +379,12 @@ def run_ours(args):
                             "median_abs_err_vs_truth": np.median(np.abs(r["x"] - truth.cpu().numpy()), 0).tolist()}}
         if cpu:
             line["cpu_baseline"] = cpu
+        if world == 1:
+            try:
+                line["other_paths"] = other_paths(zh, eng, dev)
+            except Exception as e:  # the headline line must not depend on the side measurements
+                line["other_paths"] = {"error": repr(e)}
+            eng.set_laser(lz)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
