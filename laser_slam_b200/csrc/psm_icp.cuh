@@ -154,33 +154,43 @@ __device__ __forceinline__ float pm_icp(const Sh &s, const LaserDev &L, float po
             if (s.lastpos[j] == i) { s.ix[j] = s.fx[i]; s.iy[j] = s.fy[i]; }
         }
         __syncthreads();
-        // means and cross sums, sequentially in list order: lanes 0..3 of warp 0
-        if (t < 32) {
-            float acc = 0;
-            if (t < 4)
-                for (int i = 0; i < kept; i++) {
-                    const int a = s.pairs[i] & 0xffff, j = s.pairs[i] >> 16;
-                    acc += t == 0 ? s.nx[a] : t == 1 ? s.ny[a] : t == 2 ? s.ix[j] : s.iy[j];
+        // means and cross sums are running float sums in list order: all threads gather / evaluate the terms (a product
+        // is rounded to float before it is added, as in the reference), then lanes 0..3 of warp 0 each add one array
+        {
+            float *g0 = s.pr, *g1 = s.pfi, *g2 = s.err, *g3 = s.tmpd;  // scratch that is free at this point
+            for (int i = t; i < kept; i += T) {
+                const int a = s.pairs[i] & 0xffff, j = s.pairs[i] >> 16;
+                g0[i] = s.nx[a]; g1[i] = s.ny[a]; g2[i] = s.ix[j]; g3[i] = s.iy[j];
+            }
+            __syncthreads();
+            if (t < 32) {
+                float acc = 0;
+                if (t < 4) acc = seq_sum(t == 0 ? g0 : t == 1 ? g1 : t == 2 ? g2 : g3, kept);
+                acc /= (float)kept;
+                if (t < 4) s.ctl[8 + t] = acc;
+            }
+            __syncthreads();
+            const float meanpx = s.ctl[8], meanpy = s.ctl[9], meanppx = s.ctl[10], meanppy = s.ctl[11];
+            for (int i = t; i < kept; i += T) {
+                const float px = g0[i] - meanpx, py = g1[i] - meanpy, qx = g2[i] - meanppx, qy = g3[i] - meanppy;
+                g0[i] = px * qx;  // Sxx
+                g1[i] = px * qy;  // Sxy
+                g2[i] = py * qx;  // Syx
+                g3[i] = py * qy;  // Syy
+            }
+            __syncthreads();
+            if (t < 32) {
+                float sacc = 0;
+                if (t < 4) sacc = seq_sum(t == 0 ? g0 : t == 1 ? g1 : t == 2 ? g2 : g3, kept);
+                const float sxx = __shfl_sync(0xffffffffu, sacc, 0), sxy = __shfl_sync(0xffffffffu, sacc, 1);
+                const float syx = __shfl_sync(0xffffffffu, sacc, 2), syy = __shfl_sync(0xffffffffu, sacc, 3);
+                if (t == 0) {
+                    const float ddth = zhm::atan2f_glibc(sxy - syx, sxx + syy);
+                    const float c = zhm::cosf_glibc(ddth), sn = zhm::sinf_glibc(ddth);
+                    const float ddx = meanppx - ax - (c * (meanpx - ax) - sn * (meanpy - ay));
+                    const float ddy = meanppy - ay - (sn * (meanpx - ax) + c * (meanpy - ay));
+                    s.ctl[0] = ddx; s.ctl[1] = ddy; s.ctl[2] = ddth;
                 }
-            acc /= (float)kept;
-            const float meanpx = __shfl_sync(0xffffffffu, acc, 0), meanpy = __shfl_sync(0xffffffffu, acc, 1);
-            const float meanppx = __shfl_sync(0xffffffffu, acc, 2), meanppy = __shfl_sync(0xffffffffu, acc, 3);
-            float sacc = 0;
-            if (t < 4)
-                for (int i = 0; i < kept; i++) {
-                    const int a = s.pairs[i] & 0xffff, j = s.pairs[i] >> 16;
-                    const float u = (t < 2 ? s.nx[a] - meanpx : s.ny[a] - meanpy);
-                    const float v = ((t & 1) == 0 ? s.ix[j] - meanppx : s.iy[j] - meanppy);
-                    sacc += u * v;
-                }
-            const float sxx = __shfl_sync(0xffffffffu, sacc, 0), sxy = __shfl_sync(0xffffffffu, sacc, 1);
-            const float syx = __shfl_sync(0xffffffffu, sacc, 2), syy = __shfl_sync(0xffffffffu, sacc, 3);
-            if (t == 0) {
-                const float ddth = zhm::atan2f_glibc(sxy - syx, sxx + syy);
-                const float c = zhm::cosf_glibc(ddth), sn = zhm::sinf_glibc(ddth);
-                const float ddx = meanppx - ax - (c * (meanpx - ax) - sn * (meanpy - ay));
-                const float ddy = meanppy - ay - (sn * (meanpx - ax) + c * (meanpy - ay));
-                s.ctl[0] = ddx; s.ctl[1] = ddy; s.ctl[2] = ddth;
             }
         }
         __syncthreads();

@@ -55,39 +55,57 @@ __device__ __forceinline__ float orientation_search(const Sh &s, const LaserDev 
     return r;
 }
 
-// pm_translation_estimation (ZHPolar_Match.cpp:1015-1131).  Whole-CTA call; lanes 0..6 of warp 0 each own one of the
-// reference's running sums (abs_err, n, hw1, hw2, hwh11, hwh12, hwh22) and add in beam order.
+// One lane adds arr[0..n) to a running float sum strictly in index order (the reference's order); the loads do not
+// depend on the sum, so they are issued four at a time and only the FADD chain is serial.
+__device__ __forceinline__ float seq_sum(const float *arr, int n) {
+    float acc = 0;
+    int i = 0;
+    for (; i + 4 <= n; i += 4) {
+        const float a = arr[i], b = arr[i + 1], c = arr[i + 2], d = arr[i + 3];
+        acc += a; acc += b; acc += c; acc += d;
+    }
+    for (; i < n; i++) acc += arr[i];
+    return acc;
+}
+
+// pm_translation_estimation (ZHPolar_Match.cpp:1015-1131).  Whole-CTA call.  The reference keeps seven running float
+// sums over the beams (abs_err, n, hw1, hw2, hwh11, hwh12, hwh22).  All threads first evaluate the per-beam terms
+// (products are rounded to float before they are added, exactly as `hw1 += hwi1*dr` does; a beam that fails the
+// association test contributes +0.0f, which leaves a running sum that started at +0 unchanged), then lanes 0..5 of
+// warp 0 each add one term array in beam order; the count is an integer and order-free.
 __device__ __forceinline__ float translation_estimation(const Sh &s, const LaserDev &L, float C, float *dx, float *dy,
                                                         int *status) {
     const int n = L.n, t = threadIdx.x;
+    float *t0 = s.nx, *t1 = s.ny, *t2 = s.refx, *t3 = s.refy, *t4 = s.actx, *t5 = s.acty;  // pm_icp's arrays are free here
+    if (t == 0) s.scan[0] = 0;
+    __syncthreads();
+    int mine = 0;
+    for (int i = t; i < n; i += T) {
+        const float dr = s.ref_r[i] - s.new_r[i];
+        const bool ok = s.ref_bad[i] == 0 && s.new_bad[i] == 0 && s.new_r[i] < (float)L.max_range_cm && s.new_r[i] > 10.0f &&
+                        fabsf(dr) < 100.0f;
+        const float w = C / (dr * dr + C);
+        const float hi1 = s.co[i], hi2 = s.si[i];
+        const float hwi1 = hi1 * w, hwi2 = hi2 * w;
+        t0[i] = fabsf(dr);
+        t1[i] = ok ? hwi1 * dr : 0.0f;
+        t2[i] = ok ? hwi2 * dr : 0.0f;
+        t3[i] = ok ? hwi1 * hi1 : 0.0f;
+        t4[i] = ok ? hwi1 * hi2 : 0.0f;
+        t5[i] = ok ? hwi2 * hi2 : 0.0f;
+        mine += ok;
+    }
+    mine = __reduce_add_sync(0xffffffffu, mine);
+    if ((t & 31) == 0 && mine) atomicAdd(&s.scan[0], mine);
+    __syncthreads();
     if (t < 32) {
         float acc = 0;
-        int cnt = 0;
-        if (t < 7) {
-            for (int i = 0; i < n; i++) {
-                const float dr = s.ref_r[i] - s.new_r[i];
-                if (t == 0) { acc += fabsf(dr); continue; }
-                if (s.ref_bad[i] == 0 && s.new_bad[i] == 0 && s.new_r[i] < (float)L.max_range_cm && s.new_r[i] > 10.0f &&
-                    fabsf(dr) < 100.0f) {
-                    const float w = C / (dr * dr + C);
-                    const float hi1 = s.co[i], hi2 = s.si[i];
-                    const float hwi1 = hi1 * w, hwi2 = hi2 * w;
-                    switch (t) {
-                        case 1: cnt++; break;
-                        case 2: acc += hwi1 * dr; break;
-                        case 3: acc += hwi2 * dr; break;
-                        case 4: acc += hwi1 * hi1; break;
-                        case 5: acc += hwi1 * hi2; break;
-                        default: acc += hwi2 * hi2; break;
-                    }
-                }
-            }
-        }
+        if (t < 6) acc = seq_sum(t == 0 ? t0 : t == 1 ? t1 : t == 2 ? t2 : t == 3 ? t3 : t == 4 ? t4 : t5, n);
         const float abs_err = __shfl_sync(0xffffffffu, acc, 0);
-        const int nn = __shfl_sync(0xffffffffu, cnt, 1);
-        const float hw1 = __shfl_sync(0xffffffffu, acc, 2), hw2 = __shfl_sync(0xffffffffu, acc, 3);
-        const float hwh11 = __shfl_sync(0xffffffffu, acc, 4), hwh12 = __shfl_sync(0xffffffffu, acc, 5);
-        const float hwh22 = __shfl_sync(0xffffffffu, acc, 6);
+        const float hw1 = __shfl_sync(0xffffffffu, acc, 1), hw2 = __shfl_sync(0xffffffffu, acc, 2);
+        const float hwh11 = __shfl_sync(0xffffffffu, acc, 3), hwh12 = __shfl_sync(0xffffffffu, acc, 4);
+        const float hwh22 = __shfl_sync(0xffffffffu, acc, 5);
+        const int nn = s.scan[0];
         if (t == 0) {
             int st = ST_OK;
             float ddx = 0, ddy = 0, ret = 0;

@@ -50,7 +50,11 @@ def main():
     hi = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
     hdr = rows[hi]
     col = {h: i for i, h in enumerate(hdr)}
-    body = [r for r in rows[hi + 1:] if len(r) == len(hdr)]
+    which = int(os.environ.get("NCU_LAUNCH", "0"))  # a report with several launches repeats the header per launch
+    heads = [i for i, r in enumerate(rows) if r and r[0] == "Address"]
+    hi = heads[min(which, len(heads) - 1)]
+    end = heads[heads.index(hi) + 1] if heads.index(hi) + 1 < len(heads) else len(rows)
+    body = [r for r in rows[hi + 1:end] if len(r) == len(hdr) and r[0] != "Address"]
     dis = disasm_lines(so, ksub)
     # group disassembly per function, index by offset
     per_func = collections.defaultdict(dict)
