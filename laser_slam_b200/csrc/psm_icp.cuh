@@ -37,17 +37,22 @@ __device__ __forceinline__ void bubble_passes(const Sh &s, int n, int imax) {
         float cd = 0;
         int cp = 0;
         const int steps = 2 * 31 + (n - g) + 1;
+        // one instruction stream for all lanes (no divergent paths): j == 0 loads the carry, 1 <= j < m compares the
+        // next element with the carry and stores the smaller one behind, j == m stores the carry (the element beyond the
+        // end is read as +inf, so the same min/max logic writes the carry)
         for (int tau = 0; tau < steps; tau++) {
             const int j = tau - 2 * lane;
-            if (active && m >= 1) {
-                if (j == 0) { cd = s.dist[0]; cp = s.pairs[0]; }
-                else if (j >= 1 && j < m) {
-                    const float vd = s.dist[j];
-                    const int vp = s.pairs[j];
-                    if (vd < cd) { s.dist[j - 1] = vd; s.pairs[j - 1] = vp; }
-                    else { s.dist[j - 1] = cd; s.pairs[j - 1] = cp; cd = vd; cp = vp; }
-                } else if (j == m) { s.dist[m - 1] = cd; s.pairs[m - 1] = cp; }
-            }
+            const bool in_range = active && j >= 0 && j <= m;
+            const bool has_in = in_range && j < m;
+            const int jj = has_in ? j : 0;
+            float vd = s.dist[jj];
+            int vp = s.pairs[jj];
+            if (!has_in) vd = __int_as_float(0x7f800000);
+            const bool lt = vd < cd;
+            const float wd = lt ? vd : cd;
+            const int wp = lt ? vp : cp;
+            if (in_range && j >= 1) { s.dist[j - 1] = wd; s.pairs[j - 1] = wp; }
+            if (in_range && (j == 0 || !lt)) { cd = vd; cp = vp; }
             __syncwarp();
         }
     }
