@@ -63,7 +63,7 @@ struct Match {
 
 // CPointsMap::computeMatchingWith2D.  Whole-CTA call; the result is valid on every thread and s.list / s.qj / s.qd
 // describe the kept correspondences (query q = list[k], current-cloud index offset + q*dec, map index qj[q]).
-__device__ __noinline__ Match compute_matching(const Sh &s, int N1, int N2, double px, double py, double pphi,
+__device__ __forceinline__ Match compute_matching(const Sh &s, int N1, int N2, double px, double py, double pphi,
                                                float maxDist, float maxAng, int keep_closest, int dec, int offset,
                                                const float gbox[4]) {
     const int t = threadIdx.x, lane = t & 31, w = t >> 5;
@@ -175,7 +175,7 @@ __device__ __forceinline__ double parab_deriv(double w1, double q1, double w2, d
 
 #define SQD(x) ((x) * (x))
 
-__global__ void __launch_bounds__(T) icp_kernel(IcpArgs a) {
+__global__ void __launch_bounds__(T, 3) icp_kernel(IcpArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const Sh s = carve(smem_raw, a.cap);
     const int job = blockIdx.x, t = threadIdx.x, lane = t & 31, w = t >> 5;
@@ -221,24 +221,36 @@ __global__ void __launch_bounds__(T) icp_kernel(IcpArgs a) {
             ratio = m.ratio;
             if (!nCorr) keep = false;
             else {
-                // leastSquareErrorRigidTransformation: lanes 0..7 own SumXa SumYa SumXb SumYb Sxx Sxy Syx Syy
+                // leastSquareErrorRigidTransformation: eight running float sums (SumXa SumYa SumXb SumYb Sxx Sxy Syx Syy)
+                // in correspondence order.  All threads gather the points and evaluate the products (rounded to float
+                // before they are added, as the reference's `Sxx += xa * xb` does); lanes 0..7 of warp 0 each add one
+                // array in order.
+                {
+                    const size_t ca = (size_t)((a.cap + 3) & ~3);
+                    float *tb = (float *)s.D;  // 6 arrays fit in the covariance scratch; qx / qy are free after matching
+                    for (int k = t; k < nCorr; k += T) {
+                        const int q = s.list[k], j = s.qj[q], i = offset + q * dec;
+                        const float xa = s.m1x[j], ya = s.m1y[j], xb = s.m2x[i], yb = s.m2y[i];
+                        tb[k] = xa; tb[ca + k] = ya; tb[2 * ca + k] = xb; tb[3 * ca + k] = yb;
+                        tb[4 * ca + k] = xa * xb; tb[5 * ca + k] = xa * yb;
+                        s.qx[k] = ya * xb; s.qy[k] = ya * yb;
+                    }
+                    __syncthreads();
+                }
                 if (w == 0) {
                     float acc = 0;
-                    if (lane < 8)
-                        for (int k = 0; k < nCorr; k++) {
-                            const int q = s.list[k], j = s.qj[q], i = offset + q * dec;
-                            const float xa = s.m1x[j], ya = s.m1y[j], xb = s.m2x[i], yb = s.m2y[i];
-                            switch (lane) {
-                                case 0: acc += xa; break;
-                                case 1: acc += ya; break;
-                                case 2: acc += xb; break;
-                                case 3: acc += yb; break;
-                                case 4: acc += xa * xb; break;
-                                case 5: acc += xa * yb; break;
-                                case 6: acc += ya * xb; break;
-                                default: acc += ya * yb; break;
-                            }
+                    if (lane < 8) {
+                        const size_t ca = (size_t)((a.cap + 3) & ~3);
+                        const float *arr = lane < 6 ? (const float *)s.D + lane * ca : (lane == 6 ? s.qx : s.qy);
+                        float r0 = 0;
+                        int k = 0;
+                        for (; k + 4 <= nCorr; k += 4) {
+                            const float v0 = arr[k], v1 = arr[k + 1], v2 = arr[k + 2], v3 = arr[k + 3];
+                            r0 += v0; r0 += v1; r0 += v2; r0 += v3;
                         }
+                        for (; k < nCorr; k++) r0 += arr[k];
+                        acc = r0;
+                    }
                     const float SumXa = __shfl_sync(0xffffffffu, acc, 0), SumYa = __shfl_sync(0xffffffffu, acc, 1);
                     const float SumXb = __shfl_sync(0xffffffffu, acc, 2), SumYb = __shfl_sync(0xffffffffu, acc, 3);
                     const float Sxx = __shfl_sync(0xffffffffu, acc, 4), Sxy = __shfl_sync(0xffffffffu, acc, 5);
