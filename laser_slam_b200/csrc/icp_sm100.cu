@@ -25,7 +25,8 @@ namespace icp {
 constexpr int T = 256;
 
 struct Sh {
-    float *m1x, *m1y, *m2x, *m2y;  // [cap] map cloud, current cloud
+    float2 *m1;                    // [cap] map cloud (x, y) interleaved: one 64-bit load per candidate in the search
+    float *m2x, *m2y;              // [cap] current cloud
     float *qx, *qy, *qd;           // [cap] transformed query point, squared error of its match (-1: gated out)
     int *qj;                       // [cap] matched map index
     unsigned *best;                // [cap] per map point: min squared error (float bits) among its matches
@@ -38,7 +39,7 @@ struct Sh {
 
 __host__ __device__ inline size_t sh_bytes(int cap) {
     const size_t a = (size_t)((cap + 3) & ~3);
-    return a * 4 * 10 + a * 24 + 16 * 8 + 4 * (T / 32) * 4 + 8 * 4 + 32;
+    return a * 4 * 10 + a * 24 + 16 * 8 + 4 * (T / 32) * 4 + 8 * 4 + 32;  // m1 (8) + 5 float + qj, best, list (4 each) = 40
 }
 
 __device__ inline Sh carve(unsigned char *p, int cap) {
@@ -46,8 +47,9 @@ __device__ inline Sh carve(unsigned char *p, int cap) {
     Sh s;
     s.D = (double *)p; p += a * 24;
     s.ctl = (double *)p; p += 16 * 8;
-    float **fl[] = {&s.m1x, &s.m1y, &s.m2x, &s.m2y, &s.qx, &s.qy, &s.qd};
-    for (int k = 0; k < 7; k++) { *fl[k] = (float *)p; p += a * 4; }
+    s.m1 = (float2 *)p; p += a * 8;
+    float **fl[] = {&s.m2x, &s.m2y, &s.qx, &s.qy, &s.qd};
+    for (int k = 0; k < 5; k++) { *fl[k] = (float *)p; p += a * 4; }
     s.qj = (int *)p; p += a * 4;
     s.best = (unsigned *)p; p += a * 4;
     s.list = (int *)p; p += a * 4;
@@ -94,38 +96,53 @@ __device__ __forceinline__ Match compute_matching(const Sh &s, int N1, int N2, d
     }
     if (lxmin > gbox[1] || lxmax < gbox[0] || lymin > gbox[3] || lymax < gbox[2]) { __syncthreads(); return m; }
     const int nq = offset < N2 ? (N2 - offset + dec - 1) / dec : 0;
-    // nearest neighbour + gate
+    // nearest neighbour + gate.  A thread searches TWO queries at once over its share of the map (each map point is
+    // loaded once and used twice); `parts` threads share a query pair and combine (distance, index) lexicographically.
+    const int nqp = (nq + 1) / 2;
     int parts = 1;
-    while (parts < 8 && nq * parts * 2 <= T) parts *= 2;
-    const int qper = T / parts;  // queries per round
-    for (int q0 = 0; q0 < nq; q0 += qper) {
-        const int q = q0 + t / parts, part = t % parts;
-        float bd = FLT_MAX;
-        int bj = 0x7fffffff;
-        if (q < nq) {
-            const float x = s.qx[q], y = s.qy[q];
+    while (parts < 8 && nqp * parts * 2 <= T) parts *= 2;
+    const int qper = T / parts;  // query pairs per round
+    for (int q0 = 0; q0 < nqp; q0 += qper) {
+        const int qp = q0 + t / parts, part = t % parts;
+        const int qa = 2 * qp, qb = 2 * qp + 1;
+        float bda = FLT_MAX, bdb = FLT_MAX;
+        int bja = 0x7fffffff, bjb = 0x7fffffff;
+        if (qa < nq) {
+            const float xa = s.qx[qa], ya = s.qy[qa];
+            const float xb = qb < nq ? s.qx[qb] : xa, yb = qb < nq ? s.qy[qb] : ya;
             const int per = (N1 + parts - 1) / parts;
             const int j0 = part * per, j1 = min(N1, j0 + per);
+#pragma unroll 4
             for (int j = j0; j < j1; j++) {
-                const float dx = s.m1x[j] - x, dy = s.m1y[j] - y;
-                const float d = dx * dx + dy * dy;
-                if (d < bd) { bd = d; bj = j; }
+                const float2 mp = s.m1[j];
+                const float dxa = mp.x - xa, dya = mp.y - ya, dxb = mp.x - xb, dyb = mp.y - yb;
+                const float da = dxa * dxa + dya * dya, db = dxb * dxb + dyb * dyb;
+                if (da < bda) { bda = da; bja = j; }
+                if (db < bdb) { bdb = db; bjb = j; }
             }
         }
         for (int o = 1; o < parts; o <<= 1) {
-            const float od = __shfl_xor_sync(0xffffffffu, bd, o);
-            const int oj = __shfl_xor_sync(0xffffffffu, bj, o);
-            if (od < bd || (od == bd && oj < bj)) { bd = od; bj = oj; }
+            const float oda = __shfl_xor_sync(0xffffffffu, bda, o), odb = __shfl_xor_sync(0xffffffffu, bdb, o);
+            const int oja = __shfl_xor_sync(0xffffffffu, bja, o), ojb = __shfl_xor_sync(0xffffffffu, bjb, o);
+            if (oda < bda || (oda == bda && oja < bja)) { bda = oda; bja = oja; }
+            if (odb < bdb || (odb == bdb && ojb < bjb)) { bdb = odb; bjb = ojb; }
         }
-        if (q < nq && part == 0) {
-            if (bj == 0x7fffffff) bj = 0;
-            const float x = s.qx[q], y = s.qy[q];
-            const double ex = px - x, ey = py - y;
-            const double lim = maxAng * sqrt(ex * ex + ey * ey) + maxDist;
-            const bool pass = bd < lim * lim;
-            s.qd[q] = pass ? bd : -1.f;
-            s.qj[q] = bj;
-            if (pass) s.best[bj] = 0x7f7fffffu;
+        if (part == 0) {
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                const int q = h ? qb : qa;
+                if (q >= nq) continue;
+                const float bd = h ? bdb : bda;
+                int bj = h ? bjb : bja;
+                if (bj == 0x7fffffff) bj = 0;
+                const float x = s.qx[q], y = s.qy[q];
+                const double ex = px - x, ey = py - y;
+                const double lim = maxAng * sqrt(ex * ex + ey * ey) + maxDist;
+                const bool pass = bd < lim * lim;
+                s.qd[q] = pass ? bd : -1.f;
+                s.qj[q] = bj;
+                if (pass) s.best[bj] = 0x7f7fffffu;
+            }
         }
     }
     __syncthreads();
@@ -186,7 +203,7 @@ __global__ void __launch_bounds__(T, 3) icp_kernel(IcpArgs a) {
     float gxmin = FLT_MAX, gxmax = -FLT_MAX, gymin = FLT_MAX, gymax = -FLT_MAX;
     for (int j = t; j < N1; j += T) {
         const float x = g1[j], y = g1[N1 + j];
-        s.m1x[j] = x; s.m1y[j] = y;
+        s.m1[j] = make_float2(x, y);
         gxmin = fminf(gxmin, x); gxmax = fmaxf(gxmax, x); gymin = fminf(gymin, y); gymax = fmaxf(gymax, y);
     }
     for (int i = t; i < N2; i += T) { s.m2x[i] = g2[i]; s.m2y[i] = g2[N2 + i]; }
@@ -230,7 +247,7 @@ __global__ void __launch_bounds__(T, 3) icp_kernel(IcpArgs a) {
                     float *tb = (float *)s.D;  // 6 arrays fit in the covariance scratch; qx / qy are free after matching
                     for (int k = t; k < nCorr; k += T) {
                         const int q = s.list[k], j = s.qj[q], i = offset + q * dec;
-                        const float xa = s.m1x[j], ya = s.m1y[j], xb = s.m2x[i], yb = s.m2y[i];
+                        const float xa = s.m1[j].x, ya = s.m1[j].y, xb = s.m2x[i], yb = s.m2y[i];
                         tb[k] = xa; tb[ca + k] = ya; tb[2 * ca + k] = xb; tb[3 * ca + k] = yb;
                         tb[4 * ca + k] = xa * xb; tb[5 * ca + k] = xa * yb;
                         s.qx[k] = ya * xb; s.qy[k] = ya * yb;
@@ -301,7 +318,7 @@ __global__ void __launch_bounds__(T, 3) icp_kernel(IcpArgs a) {
         const double Axy = o.Axy_aprox_derivatives, rho2 = (double)o.kernel_rho * o.kernel_rho;
         for (int k = t; k < nCorr; k += T) {
             const int q = s.list[k], j = s.qj[q], i = last_offset + q * dec;
-            const float tx = s.m1x[j], ty = s.m1y[j], ox = s.m2x[i], oy = s.m2y[i];
+            const float tx = s.m1[j].x, ty = s.m1[j].y, ox = s.m2x[i], oy = s.m2y[i];
             const float oxt = (float)(mx + ccos * ox - csin * oy);
             const float oyt = (float)(my + csin * ox + ccos * oy);
             double w1, w2, w3, q1, q2, q3;
