@@ -1,0 +1,106 @@
+"""BASELINE's full sizes through size-independent properties (the oracle cannot finish 1 M pairs in seconds):
+  * determinism: two runs over the same batch give byte-identical result records (checksum of the records);
+  * independence: matching a permuted job list gives the permuted records (no state leaks between jobs, no dependence
+    on which CTA / SM a job lands on);
+  * device-pointer path == host-pointer path through the C ABI on a slice;
+  * the recovered poses agree with the generator's ground truth (the noise floor of 1 cm range noise);
+  * a sample of the batch still agrees with the CPU oracle (the parity bar proper)."""
+import zlib
+
+import numpy as np
+import pytest
+import torch
+
+import bench
+import laser_slam_b200 as zh
+from oracle import pyoracle as po
+
+pytestmark = pytest.mark.gpu
+
+
+def _crc(t):
+    return zlib.crc32(t.cpu().numpy().tobytes())
+
+
+def test_plicp_one_million_pairs(engine):
+    lz = bench.make_laser(zh)
+    engine.set_laser(lz)
+    dev = torch.device("cuda:0")
+    P, n = 1_000_000, lz.n
+    scans = torch.empty((2 * P, n), dtype=torch.float32, device=dev)
+    truth = torch.empty((P, 3), dtype=torch.float64, device=dev)
+    engine.synth_pairs(scans, truth, 0, P, seed=bench.SEED)
+    engine.median_filter(scans)
+    ri = torch.arange(0, 2 * P, 2, dtype=torch.int32, device=dev)
+    res1 = torch.zeros((P, 128), dtype=torch.uint8, device=dev)
+    res2 = torch.zeros((P, 128), dtype=torch.uint8, device=dev)
+    engine.plicp(scans, ri, ri + 1, results=res1)
+    engine.plicp(scans, ri, ri + 1, results=res2)
+    engine.sync()
+    assert _crc(res1) == _crc(res2)                                   # determinism
+    perm = torch.randperm(P, device=dev, generator=torch.Generator(device=dev).manual_seed(1))
+    rp = ri[perm].contiguous()
+    engine.plicp(scans, rp, rp + 1, results=res2)
+    engine.sync()
+    assert torch.equal(res2, res1[perm])                              # independence of jobs
+    r = res1.cpu().numpy().view(zh.RESULT_DTYPE).reshape(-1)
+    assert (r["valid"] == 1).mean() > 0.9999
+    err = np.abs(r["x"] - truth.cpu().numpy())
+    ok = (err[:, 0] < 0.02) & (err[:, 1] < 0.02) & (err[:, 2] < 0.005)
+    assert ok.mean() > 0.995, ok.mean()
+    assert np.median(err, 0).max() < 2e-3
+    # host-pointer path on a slice == device-pointer path
+    K = 4096
+    h = scans[: 2 * K].cpu().numpy()
+    rh = engine.plicp(h, np.arange(0, 2 * K, 2), np.arange(1, 2 * K, 2))
+    assert np.array_equal(rh.view(np.uint8).reshape(K, 128), res1[:K].cpu().numpy())
+    # oracle on a sample spread over the batch
+    idx = np.linspace(0, P - 1, 512).astype(np.int64)
+    hs = torch.stack([scans[2 * idx], scans[2 * idx + 1]], 1).reshape(-1, n).cpu().numpy()
+    o = po.zhcsm_fmatch_batch(hs, np.arange(0, 1024, 2), np.arange(1, 1024, 2), lz.fi_min, lz.dfi, lz.min_range_cm,
+                              lz.max_range_cm, nthreads=8)
+    g = r[idx]
+    d = np.abs(g["x"] - o["x"])
+    assert (g["valid"] == o["valid"]).all()
+    assert ((d[:, 0] <= 1e-4) & (d[:, 1] <= 1e-4) & (d[:, 2] <= 1e-5)).mean() >= 0.998
+    assert (g["iterations"] == o["iterations"]).mean() >= 0.998
+    assert (g["corr_hash"] == o["corr_hash"]).mean() >= 0.998
+
+
+def test_icp_quarter_million_jobs(engine):
+    import os
+    d = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "zhicp_nodes.npz"))
+    dev = torch.device("cuda:0")
+    P, G, rep = d["pairs"].shape[0], 64, 64
+    rng = np.random.default_rng(3)
+    init = (d["init"][None, :, None, :] + rng.normal(0, 1, (rep, P, G, 3)) * [0.2, 0.2, 0.08]).reshape(-1, 3)
+    ri = np.tile(np.repeat(d["pairs"][:, 0], G), rep).astype(np.int32)
+    ci = np.tile(np.repeat(d["pairs"][:, 1], G), rep).astype(np.int32)
+    B = ri.size
+    assert B > 250_000
+    pts = torch.from_numpy(d["pts"]).to(dev)
+    dri, dci, dinit = torch.from_numpy(ri).to(dev), torch.from_numpy(ci).to(dev), torch.from_numpy(init).to(dev)
+    r1 = torch.zeros((B, 128), dtype=torch.uint8, device=dev)
+    r2 = torch.zeros((B, 128), dtype=torch.uint8, device=dev)
+    engine.icp(pts, d["off"], d["cnt"], dri, dci, dinit, results=r1)
+    engine.icp(pts, d["off"], d["cnt"], dri, dci, dinit, results=r2)
+    engine.sync()
+    assert _crc(r1) == _crc(r2)
+    perm = torch.randperm(B, device=dev, generator=torch.Generator(device=dev).manual_seed(2))
+    engine.icp(pts, d["off"], d["cnt"], dri[perm].contiguous(), dci[perm].contiguous(), dinit[perm].contiguous(), results=r2)
+    engine.sync()
+    assert torch.equal(r2, r1[perm])
+    best, rec = engine.best_of_starts(r1, P * rep, G)
+    r = r1.cpu().numpy().view(zh.RESULT_DTYPE).reshape(P * rep, G)
+    b = best.cpu().numpy()
+    gv = np.where(r["valid"] == 1, r["goodness"], -np.inf)            # a start without correspondences keeps MRPT's
+    has = np.isfinite(gv.max(1))                                       # initial goodness 1 and is not a candidate
+    assert (b[~has] == -1).all() and (b[has] >= 0).all()
+    assert (gv[np.arange(P * rep), np.maximum(b, 0)][has] == gv.max(1)[has]).all()
+    # oracle on a sample
+    idx = np.linspace(0, B - 1, 1024).astype(np.int64)
+    o = po.mrpt_icp_batch(d["pts"], d["off"], d["cnt"], ri[idx], ci[idx], init[idx], nthreads=8)
+    g = r.reshape(-1)[idx]
+    dp = np.abs(g["x"] - o["pose"])
+    ok = (dp[:, 0] <= 1e-4) & (dp[:, 1] <= 1e-4) & (dp[:, 2] <= 1e-5) & (g["iterations"] == o["nIterations"])
+    assert ok.mean() >= 0.98, ok.mean()
