@@ -44,10 +44,15 @@ print(f"C5: {P} pairs x {G} starts = {P*G} matches (n={n}) in {dt*1e3:.1f} ms (k
       f"{P/dt:.0f} pairs/s; best_of_starts {dtb*1e3:.2f} ms")
 print(f"    valid starts {r['valid'].mean():.3f}; iterations/start {r['iterations'].mean():.1f}; pairs with best start within 2 cm / 0.5 deg of truth: "
       f"{ok.mean():.4f} (any start: {ok_any.any(1).mean():.4f}; single start nearest odometry: {ok_any[:, 0].mean():.4f})")
+w = r["reserved"].astype(np.float64)
+print(f"    walks per start: {w[..., 0].mean():.0f} executed for {w[..., 1].mean():.0f} sequential ({w[..., 0].sum() / w[..., 1].sum():.2f}x); "
+      f"re-search warp rounds {w[..., 2].mean():.0f}; kernel {kms / (P * G) * 148 * 1e3:.0f} us of SM time per start")
 # parity sample against the CPU restatement
 K = 512
 fm = scans[: 2 * (K // G)].cpu().numpy()
+t = time.time()
 o = po.zhcsm_fmatch_batch(fm, ri[:K], si[:K], lz.fi_min, lz.dfi, 10, 3000, first_guess=guess[:K], nthreads=os.cpu_count())
+print(f"    oracle: {K} starts on {os.cpu_count()} threads in {time.time() - t:.2f} s -> {K / (time.time() - t):.0f} matches/s")
 rr = r.reshape(-1)[:K]
 dp = np.abs(rr["x"] - o["x"])
 both = (rr["valid"] == 1) & (o["valid"] == 1)
