@@ -8,45 +8,64 @@
 
 // ---------------------------------------------------------------------------------------------------------
 // 5-tap in-place median filter: CCanonicalMatcher::median_filter (src/zhcsm/ZHCanonical_Matcher.cpp:159-189)
-// == CPolarMatch::pm_median_filter (src/zhpsm/ZHPolar_Match.cpp:1610-1639).  The write-back makes taps i-2,i-1
-// already-filtered values, i.e. a left-to-right recurrence: one thread walks one scan, the window lives in
-// registers.  A row is touched once (32-byte sectors are reused by the walking thread through L1).
+// == CPolarMatch::pm_median_filter (src/zhpsm/ZHPolar_Match.cpp:1610-1639).  The write-back makes taps i-2, i-1
+// already-filtered values, i.e. a left-to-right recurrence along each scan: the parallelism is across scans.
+// HBM-bound (8 B per beam).  A warp owns 32 scans and moves them through shared memory in tiles of 32 beams (+2 beams
+// of look-ahead): every global access is a full coalesced row segment (lane = beam), while the recurrence runs with
+// lane = scan on the transposed view (row pitch 35 floats: conflict-free).  The window lives in registers.
 // ---------------------------------------------------------------------------------------------------------
-__global__ void median_filter_kernel(float *scans, int S, int n) {
-    int sidx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (sidx >= S) return;
-    float *r = scans + (size_t)sidx * n;
-    // window = {f[i-2], f[i-1], r[i], r[i+1], r[i+2]} with clamped indices; f = filtered
-    float r0 = r[0];
-    float m2 = r0, m1 = r0;                    // taps i-2, i-1 (clamped to index 0 -> the ORIGINAL r[0] until written)
-    float c0 = r0;
-    float p1 = n > 1 ? r[1] : r0;
-    float p2 = n > 2 ? r[2] : p1;
-    for (int i = 0; i < n; i++) {
-        float w0 = m2, w1 = m1, w2 = c0, w3 = p1, w4 = p2;
-        // bubble sort is a pure compare/swap sort: any exact median-of-5 gives the same value
-        float a = w0, b = w1, c = w2, d = w3, e = w4, t;
+constexpr int MF_W = 32, MF_PITCH = MF_W + 3, MF_WARPS = 4;
+
+__device__ __forceinline__ float median5(float w0, float w1, float w2, float w3, float w4) {
+    // bubble sort is a pure compare/swap sort: any exact median-of-5 gives the same value
+    float a = w0, b = w1, c = w2, d = w3, t;
 #define ZH_SW(x, y) if (x > y) { t = x; x = y; y = t; }
-        ZH_SW(a, b) ZH_SW(c, d) ZH_SW(a, c) ZH_SW(b, d)   // a = min(a..d), d = max(a..d)
-        ZH_SW(b, c)                                       // a <= b <= c <= d
-        // insert e: median of {a,b,c,d,e} = median of {b, c, e} when a<=b<=c<=d
-        float med = e < b ? b : (e > c ? c : e);
+    ZH_SW(a, b) ZH_SW(c, d) ZH_SW(a, c) ZH_SW(b, d)   // a = min(a..d), d = max(a..d)
+    ZH_SW(b, c)                                       // a <= b <= c <= d
 #undef ZH_SW
-        r[i] = med;
-        // slide: taps for i+1 are f[i-1], f[i], r[i+1], r[i+2], r[i+3]; clamping at 0 uses f[0] once written
-        if (i == 0) { m2 = med; m1 = med; }   // indices -1 and 0 both clamp to 0, which now holds f[0]
-        else { m2 = m1; m1 = med; }
-        c0 = p1;
-        p1 = p2;
-        int nx = i + 3;
-        p2 = r[nx < n ? nx : n - 1];
-        // clamped right taps read r[n-1], still unfiltered until i reaches n-1
+    return w4 < b ? b : (w4 > c ? c : w4);            // median of {a,b,c,d,e} = median of {b, c, e}
+}
+
+__global__ void __launch_bounds__(32 * MF_WARPS) median_filter_kernel(float *scans, int S, int n) {
+    __shared__ float tile_all[MF_WARPS][32 * MF_PITCH];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float *tile = tile_all[warp];
+    const long long base = ((long long)blockIdx.x * MF_WARPS + warp) * 32;  // first scan of this warp
+    if (base >= S) return;
+    const int ns = (int)(S - base < 32 ? S - base : 32);
+    float m2 = 0, m1 = 0;  // filtered taps i-2, i-1 of scan `lane`
+    for (int c0 = 0; c0 < n; c0 += MF_W) {
+        // load: row segment [c0, c0 + 34) of each scan, indices clamped to n-1 (the reference clamps the taps)
+        for (int sc = 0; sc < ns; sc++) {
+            const float *row = scans + (size_t)(base + sc) * n;
+            const int c = c0 + lane;
+            tile[sc * MF_PITCH + lane] = row[c < n ? c : n - 1];
+            if (lane < 2) { const int c2 = c0 + MF_W + lane; tile[sc * MF_PITCH + MF_W + lane] = row[c2 < n ? c2 : n - 1]; }
+        }
+        __syncwarp();
+        if (lane < ns) {
+            float *t = tile + lane * MF_PITCH;
+            const int w = n - c0 < MF_W ? n - c0 : MF_W;
+            if (c0 == 0) { m2 = t[0]; m1 = t[0]; }  // indices -2, -1 clamp to 0: the ORIGINAL r[0] until it is written
+            for (int k = 0; k < w; k++) {
+                const float med = median5(m2, m1, t[k], t[k + 1], t[k + 2]);
+                t[k] = med;
+                // taps for i+1 are f[i-1], f[i]; at i = 0 both clamped taps now see f[0]
+                if (c0 + k == 0) { m2 = med; m1 = med; } else { m2 = m1; m1 = med; }
+            }
+        }
+        __syncwarp();
+        for (int sc = 0; sc < ns; sc++) {
+            const int c = c0 + lane;
+            if (c < n) scans[(size_t)(base + sc) * n + c] = tile[sc * MF_PITCH + lane];
+        }
+        __syncwarp();
     }
 }
 
 cudaError_t median_filter_launch(float *scans, int S, int n, cudaStream_t st) {
-    int nt = 128;
-    median_filter_kernel<<<(S + nt - 1) / nt, nt, 0, st>>>(scans, S, n);
+    const int per_block = 32 * MF_WARPS;
+    median_filter_kernel<<<(S + per_block - 1) / per_block, 32 * MF_WARPS, 0, st>>>(scans, S, n);
     return cudaGetLastError();
 }
 
