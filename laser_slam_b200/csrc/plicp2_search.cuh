@@ -76,11 +76,15 @@ static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int 
             if (now_up) up_stopped = true; else down_stopped = true;
             continue;
         }
+        // everything a step may need depends only on idx: issue all shared-memory loads up front so that their
+        // latencies overlap instead of chaining behind the comparisons (the walk is latency-bound)
         const double rr2 = rr2a[idx];
+        const double2 q = refp[idx];
+        const short *jd = jt + (now_up ? 0 : 2 * n) + idx;
+        const int hop_bigger = jd[0], hop_smaller = jd[n];
         int step = now_up ? 1 : -1;
         bool stop = false;
         if (rr2 >= 0) {
-            const double2 q = refp[idx];
             const double d = dist2(wx, wy, q.x, q.y);
             if (now_up) last_up = d; else last_down = d;
             if (d < best || j1 == -1) { j1 = idx; best = d; }
@@ -92,7 +96,7 @@ static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int 
                 const double lhs = far ? rho2 : cross * cross;
                 const double rhs = far ? best : best * rr2;
                 stop = lhs > rhs;
-                step = jt[((now_up ? 0 : 2) + (rr2 < rho2 ? 0 : 1)) * n + idx];
+                step = rr2 < rho2 ? hop_bigger : hop_smaller;
             }
         }
         if (stop) {
