@@ -17,14 +17,18 @@ def newest(paths):
     return max(os.path.getmtime(p) for p in paths)
 
 
-def build(force=False, verbose=False):
-    """Per-source objects (csrc/_obj/*.o, rebuilt only when a dependency is newer) linked into libzhsm.so."""
-    objdir = os.path.join(CSRC, "_obj")
+def build(force=False, verbose=False, variant=None, defs=()):
+    """Per-source objects (csrc/_obj/*.o, rebuilt only when a dependency is newer) linked into libzhsm.so.
+    variant/defs: a tuning build with extra -D flags into libzhsm_<variant>.so (loaded with ZHSM_LIB_VARIANT=<variant>;
+    e.g. variant="timing", defs=("PLICP_PHASE_TIMING",) for tools/gpu_probe_phases.py); never the product."""
+    objdir = os.path.join(CSRC, "_obj" + ("_" + variant if variant else ""))
+    OUT = os.path.join(HERE, "libzhsm%s.so" % ("_" + variant if variant else ""))
+    extra = ["-D" + d for d in defs]
     os.makedirs(objdir, exist_ok=True)
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))]
     headers.append(os.path.join(HERE, "..", "include", "zhsm.h"))
     ccbin = [] if not os.path.exists("/usr/bin/g++") else ["-ccbin", "/usr/bin/g++"]
-    log = os.path.join(HERE, "build.log")
+    log = os.path.join(HERE, "build%s.log" % ("_" + variant if variant else ""))
     objs, rebuilt = [], False
     procs = []
     for s in SOURCES:
@@ -32,7 +36,7 @@ def build(force=False, verbose=False):
         obj = os.path.join(objdir, s.replace(".cu", ".o"))
         objs.append(obj)
         if force or not os.path.exists(obj) or os.path.getmtime(obj) < newest([src] + headers):
-            cmd = [NVCC] + ccbin + [f for f in FLAGS if f != "-shared"] + ["-c", "-o", obj, src]
+            cmd = [NVCC] + ccbin + [f for f in FLAGS if f != "-shared"] + extra + ["-c", "-o", obj, src]
             procs.append((s, cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
             rebuilt = True
     out_all = ""

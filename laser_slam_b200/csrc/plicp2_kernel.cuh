@@ -10,6 +10,19 @@
 
 namespace plicp2 {
 
+// Per-phase cycle counters of thread 0 (tuning builds only: -DPLICP_PHASE_TIMING; the counters then REPLACE
+// x/cov/error/goodness/quality in the result record, see tools/gpu_probe_phases.py).
+struct PhaseClock {
+#ifdef PLICP_PHASE_TIMING
+    long long last, acc[12];
+    __device__ __forceinline__ void start() { for (int k = 0; k < 12; k++) acc[k] = 0; last = clock64(); }
+    __device__ __forceinline__ void mark(int k) { const long long c = clock64(); acc[k] += c - last; last = c; }
+#else
+    __device__ __forceinline__ void start() {}
+    __device__ __forceinline__ void mark(int) {}
+#endif
+};
+
 // pose of the current iteration + what make_ray needs
 struct IterCtx {
     double x0, x1, cs, sn;
@@ -30,7 +43,7 @@ __device__ __forceinline__ bool search_ray(const Lay &l, const WalkCtx &w, const
 // sens: bit k = ray k*T+t exists and is valid; returns the mask of rays holding a correspondence.
 template <int T>
 __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const WalkCtx &w, const IterCtx &it, int C,
-                                                         unsigned sens, int &nsearch, int &nround) {
+                                                         unsigned sens, int &nsearch, int &nround, PhaseClock &pc) {
     const int t = threadIdx.x;
     unsigned valid = 0;
 #pragma unroll 1
@@ -40,6 +53,7 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
             if (search_ray(l, w, it, k * T + t)) valid |= 1u << k;
         }
     __syncthreads();
+    pc.mark(2);
     const short *cj1 = PL_SH(const short, l.cj1);
     short *spec = PL_SH(short, l.spec);
     while (true) {
@@ -67,6 +81,7 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
         }
         __syncthreads();
     }
+    pc.mark(3);
     return valid;
 }
 
@@ -87,27 +102,46 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
     short *cj1 = PL_SH(short, l.cj1), *cj2 = PL_SH(short, l.cj2);
     double *red = PL_SH(double, l.red);
 
+    PhaseClock pc;
+    pc.start();
     // ---------------- load + fromPMScan2LDP + ld_valid_fields + ld_invalid_if_outside + ld_compute_cartesian
     const float *ref_row = a.scans + (size_t)a.ref_idx[job] * n;
     const float *sens_row = a.scans + (size_t)a.sens_idx[job] * n;
     int bad_field = 0, nvf_ref = 0, nvf_sens = 0;
     unsigned sens = 0;
+    const JumpAux ja = make_jump_aux(l, n);
 #pragma unroll 1
     for (int k = 0; k < C; k++) {
         const int i = k * T + t;
-        if (i >= n) break;
-        const double2 cs = a.cs[i];
-        double rr = reading_of(__ldg(ref_row + i), L, P, &bad_field);
-        nvf_ref += (rr != -1.0);
-        rr2a[i] = rr >= 0 ? rr * rr : -1.0;
-        refp[i] = rr >= 0 ? make_double2(cs.x * rr, cs.y * rr) : make_double2(nan(""), nan(""));
-        double rs = reading_of(__ldg(sens_row + i), L, P, &bad_field);
-        nvf_sens += (rs != -1.0);
-        sensp[i] = rs >= 0 ? make_double2(cs.x * rs, cs.y * rs) : make_double2(nan(""), nan(""));
-        if (rs >= 0) sens |= 1u << k;
-        cj1[i] = -1;
-        cj2[i] = -1;
-        PL_SH(short, l.spec)[i] = -1;
+        double hi = -1.0, lo = INFINITY;  // neutral for the block extrema (rays past the end of the scan)
+        if (i < n) {
+            const double2 cs = a.cs[i];
+            double rr = reading_of(__ldg(ref_row + i), L, P, &bad_field);
+            nvf_ref += (rr != -1.0);
+            const double r2 = rr >= 0 ? rr * rr : -1.0;
+            rr2a[i] = r2;
+            hi = rr >= 0 ? r2 : INFINITY;
+            lo = r2;
+            refp[i] = rr >= 0 ? make_double2(cs.x * rr, cs.y * rr) : make_double2(nan(""), nan(""));
+            double rs = reading_of(__ldg(sens_row + i), L, P, &bad_field);
+            nvf_sens += (rs != -1.0);
+            sensp[i] = rs >= 0 ? make_double2(cs.x * rs, cs.y * rs) : make_double2(nan(""), nan(""));
+            if (rs >= 0) sens |= 1u << k;
+            cj1[i] = -1;
+            cj2[i] = -1;
+            PL_SH(short, l.spec)[i] = -1;
+        }
+        // extrema of the aligned 8-ray blocks for the jump-table searches (T is a multiple of 32: lanes 8g..8g+7
+        // hold rays 8g'..8g'+7)
+#pragma unroll
+        for (int o = 1; o < 8; o <<= 1) {
+            hi = fmax(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+            lo = fmin(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+        }
+        if (i < n && (lane & 7) == 0) {
+            PL_SH(double, ja.hi8)[i >> 3] = hi;
+            PL_SH(double, ja.lo8)[i >> 3] = lo;
+        }
     }
     if (t == 0) {
         for (int k = 0; k < 3; k++) ctl->x[0][k] = a.first_guess ? a.first_guess[3 * (size_t)job + k] : 0.0;
@@ -133,8 +167,12 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
         if (oj1) for (int i = t; i < n; i += T) { oj1[i] = -1; oj2[i] = -1; }
         return;
     }
-    build_jump_tables(l, n, t, T);
+    pc.mark(0);
+    jump_aux_level2(ja, t);  // the block sums above were barriers: hi8 / lo8 are complete
     __syncthreads();
+    build_jump_tables(l, ja, n, t, T);
+    __syncthreads();
+    pc.mark(1);
 
     IterCtx it;
     it.min_theta = (double)theta_f(L.fi_min, L.dfi, 0);
@@ -161,7 +199,7 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
             it.sn = ctl->sn[par];
             for (int j = t; j < n; j += T) d2j[j] = BIG;
             if (t == 0) ctl->hash_acc[iteration & 1] = 0;
-            valid = find_correspondences<T>(l, wc, it, C, sens, nsearch, nround);
+            valid = find_correspondences<T>(l, wc, it, C, sens, nsearch, nround, pc);
             // kill_outliers_double (icp_outliers.c): min dist2_j1 per ref index.  dist2_j1 is recomputed
             // from the same operands the walk used (bit-identical), so it needs no storage.
             if (P.outliers_remove_doubles) {
@@ -194,6 +232,7 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
                 }
             }
             for (int b = t; b < 256; b += T) PL_SH(int, l.hist)[b] = 0;
+            pc.mark(4);
             const int kcnt = block_sum<T>(__popc(valid), ctl->ired, 2);  // all reads of d2j are done
             // kill_outliers_trim: distance to the segment (j1,j2); keys go to shared memory
 #pragma unroll 1
@@ -214,6 +253,7 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
             order2 = order2 > 0 ? order2 : 0;
             double lim1, d_o2;
             select2<T>(l, C, valid, order, order2, lim1, d_o2);
+            pc.mark(5);
             const double lim2 = P.outliers_adaptive_mult * d_o2;
             const double error_limit = lim1 < lim2 ? lim1 : lim2;
             // kill + per-thread partial sums: total_error, nvalid, GPC sums (compute_next_estimate + gpc_solve)
@@ -269,12 +309,14 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
                 for (int q = 0; q < NSUM - 1; q++) red[warp * NSUM + q] = S[q];
             }
             const int num_after = block_sum<T>(nkept, ctl->ired, 3);  // barrier: publishes red, cj1, cj2
+            pc.mark(6);
             // ld_corr_hash of this iteration's correspondences, in parallel
             {
                 unsigned hc = corr_hash_chunk(l, n, t, a.hash_chunk, a.hashmat);
                 hc = __reduce_xor_sync(0xffffffffu, hc);
                 if (lane == 0 && hc) atomicXor(&ctl->hash_acc[iteration & 1], hc);
             }
+            pc.mark(7);
             if (warp == 0) {
                 double v = 0;
                 if (lane < NSUM - 1)
@@ -306,6 +348,7 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
                 }
             }
             __syncthreads();
+            pc.mark(8);
             // loop control of icp_loop, evaluated identically by every thread
             const int st = ctl->solve_status;
             int brk = 0;
@@ -366,6 +409,7 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
         __syncthreads();
         if (!ctl->next) break;
     }
+    pc.mark(9);
     // ---------------- final correspondences + result record
     const int fin = ctl->fin;
     const bool v_ok = fin & 1, v_restarted = fin & 2;
@@ -382,7 +426,7 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
         it.cs = ctl->cs[0];
         it.sn = ctl->sn[0];
         // "recompute correspondences in case of restarts" (icp.c): world coords at best x + tricks, no outlier pass
-        if (v_restarted) valid = find_correspondences<T>(l, wc, it, C, sens, nsearch, nround);
+        if (v_restarted) valid = find_correspondences<T>(l, wc, it, C, sens, nsearch, nround, pc);
     }
     if (t == 0) ctl->hash_acc[0] = 0;
 #pragma unroll 1
@@ -424,6 +468,13 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
             r.corr_hash = ctl->hash_acc[0] & 0x7FFFFFFFu;
             for (int q = 0; q < 6; q++) r.cov[q] = cov[q];
         }
+#ifdef PLICP_PHASE_TIMING
+        pc.mark(10);
+        for (int k = 0; k < 3; k++) r.x[k] = (double)pc.acc[k];
+        for (int k = 0; k < 6; k++) r.cov[k] = (double)pc.acc[3 + k];
+        r.error = (double)pc.acc[9];
+        r.goodness = (float)pc.acc[10];
+#endif
         *res = r;
     }
 }

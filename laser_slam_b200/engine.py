@@ -74,7 +74,8 @@ _lib = None
 
 
 def lib_path():
-    return os.path.join(_HERE, "libzhsm.so")
+    v = os.environ.get("ZHSM_LIB_VARIANT")  # tuning builds only (laser_slam_b200.build.build(variant=...))
+    return os.path.join(_HERE, "libzhsm_%s.so" % v if v else "libzhsm.so")
 
 
 def load_library():

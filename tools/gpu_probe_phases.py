@@ -1,0 +1,29 @@
+"""Tuning probe: where one PL-ICP job spends its cycles.  Needs the timing variant of the library
+(python -c "from laser_slam_b200 import build as b; b.build(variant='timing', defs=('PLICP_PHASE_TIMING',))"),
+in which thread 0 of every CTA accumulates clock64() deltas per phase and the record's x/cov/error/goodness
+carry those counters instead of the result.  Run: ZHSM_LIB_VARIANT=timing python tools/gpu_probe_phases.py [pairs]"""
+import os, sys
+os.environ.setdefault("ZHSM_LIB_VARIANT", "timing")
+import numpy as np, torch
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
+import laser_slam_b200 as zh
+import bench
+P = int(sys.argv[1]) if len(sys.argv) > 1 else 20000
+eng = zh.Engine(0); eng.set_laser(bench.make_laser(zh))
+dev = torch.device("cuda:0")
+n = bench.N_BEAMS
+scans = torch.empty((2 * P, n), dtype=torch.float32, device=dev); truth = torch.empty((P, 3), dtype=torch.float64, device=dev)
+eng.synth_pairs(scans, truth, 0, P, seed=bench.SEED); eng.median_filter(scans)
+ri = torch.arange(0, 2 * P, 2, dtype=torch.int32, device=dev); si = ri + 1
+res = torch.zeros((P, 128), dtype=torch.uint8, device=dev)
+for _ in range(2):
+    eng.plicp(scans, ri, si, results=res); eng.sync()
+r = res.cpu().numpy().view(zh.RESULT_DTYPE).reshape(-1)
+ph = np.concatenate([r["x"], r["cov"], r["error"][:, None], r["goodness"][:, None].astype(np.float64)], axis=1)
+names = ["load", "jump tables", "first-pass walk", "verify + re-search", "kill doubles", "trim keys + select",
+         "kill + GPC sums", "corr hash", "solve (warp 0)", "loop control", "final corr/hash/cov"]
+tot = ph.sum(1)
+print(f"kernel {eng.last_kernel_ms():.2f} ms for {P} pairs; iterations/pair {r['iterations'].mean():.2f}; "
+      f"cycles/job {tot.mean():.0f} (thread 0 clock64, includes barrier waits and time-slicing with co-resident CTAs)")
+for k, nm in enumerate(names):
+    print(f"  {nm:22s} {ph[:, k].mean():10.0f} cycles/job  {100 * ph[:, k].sum() / tot.sum():5.1f} %   per iteration {ph[:, k].sum() / r['iterations'].sum():8.0f}")
