@@ -30,6 +30,7 @@ struct Ctl {
     int nvalid;         // correspondences kept by the last iteration
     int next;           // run another icp_loop
     int fin;            // valid | restarted<<1
+    int qn[2];          // re-search queue length (ping-pong over verify rounds)
 };
 
 // byte offsets into the dynamic shared memory block

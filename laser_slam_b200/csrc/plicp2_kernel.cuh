@@ -14,13 +14,19 @@ namespace plicp2 {
 // x/cov/error/goodness/quality in the result record, see tools/gpu_probe_phases.py).
 struct PhaseClock {
 #ifdef PLICP_PHASE_TIMING
-    long long last, acc[12];
-    __device__ __forceinline__ void start() { for (int k = 0; k < 12; k++) acc[k] = 0; last = clock64(); }
+    long long last, acc[16];
+    __device__ __forceinline__ void start() { for (int k = 0; k < 16; k++) acc[k] = 0; last = clock64(); }
     __device__ __forceinline__ void mark(int k) { const long long c = clock64(); acc[k] += c - last; last = c; }
 #else
     __device__ __forceinline__ void start() {}
     __device__ __forceinline__ void mark(int) {}
 #endif
+};
+
+// diagnostics of the correspondence search (zhsm_result.reserved): walks by this thread, of which first-pass walks
+// (= what the sequential algorithm executes); verify rounds that had work
+struct WalkDiag {
+    int walks, first, rounds;
 };
 
 // pose of the current iteration + what make_ray needs
@@ -40,48 +46,94 @@ __device__ __forceinline__ bool search_ray(const Lay &l, const WalkCtx &w, const
 }
 
 // find_correspondences_tricks for the whole scan: speculate / verify / re-search until the sequential result.
-// sens: bit k = ray k*T+t exists and is valid; returns the mask of rays holding a correspondence.
+// First pass: thread t walks its rays k*T+t with the last_best the previous iteration saw (spec[]).
+// Verify: last_best before ray i is j1 of the nearest earlier ray holding a correspondence -- found with warp ballots
+// inside a group of 32 consecutive rays and a table of the groups' last results across groups.  A ray whose actual
+// last_best differs from spec[] is appended to a CTA-wide queue (warp-aggregated atomicAdd), and the queue is walked
+// densely, entry e by thread e mod T (re-searched rays are sparse, about 2 of 3; queueing them fills the lanes).
+// The fixpoint is reached when no re-search changed a j1 (the usual case after one round).
+// The queue and the group table live in the d2j area; d2j itself is initialised after the search.
+// sens: bit k = ray k*T+t exists and is valid; returns the mask of those rays holding a correspondence.
 template <int T>
 __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const WalkCtx &w, const IterCtx &it, int C,
-                                                         unsigned sens, int &nsearch, int &nround, PhaseClock &pc) {
-    const int t = threadIdx.x;
-    unsigned valid = 0;
+                                                         unsigned sens, WalkDiag &dg, PhaseClock &pc) {
+    constexpr int NW = T / 32;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int n = w.n;
+    const unsigned lane_lt = (1u << lane) - 1u;
+    Ctl *ctl = PL_SH(Ctl, l.ctl);
+    if (t == 0) ctl->qn[0] = 0;
 #pragma unroll 1
     for (int k = 0; k < C; k++)
         if (sens >> k & 1u) {
-            nsearch += 0x10001;
-            if (search_ray(l, w, it, k * T + t)) valid |= 1u << k;
+            dg.walks++;
+            dg.first++;
+            search_ray(l, w, it, k * T + t);
         }
     __syncthreads();
     pc.mark(2);
-    const short *cj1 = PL_SH(const short, l.cj1);
+    short *cj1 = PL_SH(short, l.cj1);
     short *spec = PL_SH(short, l.spec);
-    while (true) {
-        unsigned need = 0;
+    short *queue = PL_SH(short, l.d2j);
+    short *glast = queue + n;  // [C][NW]: j1 of the last ray with a correspondence in each group of 32 rays, or -1
+    for (int round = 0;; round++) {
+        int *qn = &ctl->qn[round & 1];
+        if (t == 0) ctl->qn[(round + 1) & 1] = 0;
 #pragma unroll 1
         for (int k = 0; k < C; k++) {
-            if (!(sens >> k & 1u)) continue;
             const int i = k * T + t;
-            int actual = -1;
-            for (int u = i - 1; u >= 0; u--) {
-                const int v = cj1[u];
-                if (v >= 0) { actual = v; break; }
-            }
-            if (actual != (int)spec[i]) { need |= 1u << k; spec[i] = (short)actual; }
+            const int c1 = i < n ? (int)cj1[i] : -1;
+            const unsigned vm = __ballot_sync(0xffffffffu, c1 >= 0);
+            const int last = __shfl_sync(0xffffffffu, c1, vm ? 31 - __clz(vm) : 0);
+            if (lane == 0) glast[k * NW + warp] = (short)(vm ? last : -1);
         }
-        if (!__syncthreads_or((int)need)) break;
+        __syncthreads();
 #pragma unroll 1
         for (int k = 0; k < C; k++) {
-            nround += __any_sync(0xffffffffu, need >> k & 1u) ? 1 : 0;  // diagnostics: warp rounds of re-searches
-            if (need >> k & 1u) {
-                nsearch += 1;
-                if (search_ray(l, w, it, k * T + t)) valid |= 1u << k;
-                else valid &= ~(1u << k);
+            const int i = k * T + t;
+            const int c1 = i < n ? (int)cj1[i] : -1;
+            const unsigned vm = __ballot_sync(0xffffffffu, c1 >= 0);
+            const unsigned below = vm & lane_lt;
+            int actual = __shfl_sync(0xffffffffu, c1, below ? 31 - __clz(below) : 0);
+            bool need = false;
+            if (sens >> k & 1u) {
+                if (!below) {
+                    actual = -1;
+                    for (int g = k * NW + warp - 1; g >= 0; g--) {
+                        const int v = glast[g];
+                        if (v >= 0) { actual = v; break; }
+                    }
+                }
+                if (actual != (int)spec[i]) { need = true; spec[i] = (short)actual; }
+            }
+            const unsigned m = __ballot_sync(0xffffffffu, need);
+            if (m) {
+                int base = 0;
+                if (lane == 0) base = atomicAdd(qn, __popc(m));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (need) queue[base + __popc(m & lane_lt)] = (short)i;
             }
         }
         __syncthreads();
+        const int total = *qn;
+        if (total == 0) break;
+        dg.rounds++;
+        int changed = 0;
+#pragma unroll 1
+        for (int e = t; e < total; e += T) {
+            const int i = (int)queue[e];
+            const int before = cj1[i];
+            dg.walks++;
+            search_ray(l, w, it, i);
+            changed |= (int)cj1[i] != before;
+        }
+        if (!__syncthreads_or(changed)) break;  // last_best of every ray is what it was walked with
     }
     pc.mark(3);
+    unsigned valid = 0;
+#pragma unroll 1
+    for (int k = 0; k < C; k++)
+        if ((sens >> k & 1u) && cj1[k * T + t] >= 0) valid |= 1u << k;
     return valid;
 }
 
@@ -188,7 +240,7 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
     double best_x[3] = {0, 0, 0}, x_first[3] = {0, 0, 0}, best_error = 0;
     int iterations = 0, nvalid0 = 0, n_loops = 0, restarted = 0, valid_out = 0, status = ZHSM_JOB_OK;
     unsigned valid = 0;
-    int nsearch = 0, nround = 0;  // diagnostics: low 16 bits walks by this thread, high 16 first-pass walks; warp rounds
+    WalkDiag dg = {0, 0, 0};
 
     for (int loop = 0; loop < 7; loop++) {
         int iteration = 0, all_ok = 1, par = 0, newest = 0;
@@ -197,9 +249,12 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
             it.x1 = ctl->x[par][1];
             it.cs = ctl->cs[par];
             it.sn = ctl->sn[par];
-            for (int j = t; j < n; j += T) d2j[j] = BIG;
             if (t == 0) ctl->hash_acc[iteration & 1] = 0;
-            valid = find_correspondences<T>(l, wc, it, C, sens, nsearch, nround, pc);
+            valid = find_correspondences<T>(l, wc, it, C, sens, dg, pc);
+            if (P.outliers_remove_doubles) {
+                for (int j = t; j < n; j += T) d2j[j] = BIG;  // the search used this area as its queue
+                __syncthreads();
+            }
             // kill_outliers_double (icp_outliers.c): min dist2_j1 per ref index.  dist2_j1 is recomputed
             // from the same operands the walk used (bit-identical), so it needs no storage.
             if (P.outliers_remove_doubles) {
@@ -326,8 +381,10 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
                 for (int q = 0; q < NSUM - 1; q++) Tt[q] = __shfl_sync(0xffffffffu, v, q);
                 int st = 0;
                 double xn[3] = {0, 0, 0};
+                pc.mark(11);
                 if (num_after < fail_perc * n) st = ZHSM_JOB_TOO_FEW_POINTS;
-                else if (!gpc_solve_warp(Tt, xn)) st = ZHSM_JOB_SINGULAR;
+                else if (!gpc_solve_warp(Tt, xn, &pc)) st = ZHSM_JOB_SINGULAR;
+                pc.mark(15);
                 if (lane == 0) {
                     ctl->solve_status = st;
                     ctl->error = Tt[14];
@@ -426,7 +483,7 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
         it.cs = ctl->cs[0];
         it.sn = ctl->sn[0];
         // "recompute correspondences in case of restarts" (icp.c): world coords at best x + tricks, no outlier pass
-        if (v_restarted) valid = find_correspondences<T>(l, wc, it, C, sens, nsearch, nround, pc);
+        if (v_restarted) valid = find_correspondences<T>(l, wc, it, C, sens, dg, pc);
     }
     if (t == 0) ctl->hash_acc[0] = 0;
 #pragma unroll 1
@@ -444,9 +501,9 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
         if (lane == 0 && hc) atomicXor(&ctl->hash_acc[0], hc);
     }
     __syncthreads();
-    const int walks_all = block_sum<T>(nsearch & 0xffff, ctl->ired, 0);
-    const int rewalk_rounds = block_sum<T>(lane == 0 ? nround : 0, ctl->ired, 2);
-    const int walks_first = block_sum<T>(nsearch >> 16, ctl->ired, 1);
+    const int walks_all = block_sum<T>(dg.walks, ctl->ired, 0);
+
+    const int walks_first = block_sum<T>(dg.first, ctl->ired, 1);
     double cov[6] = {0, 0, 0, 0, 0, 0};
     if (v_ok && P.do_compute_covariance)
         covariance_exact<T>(l, n, C, a.cs, it.x0, it.x1, it.cs, it.sn, P.sigma, cov);
@@ -457,8 +514,8 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
         r.iterations = iterations;
         r.n_loops = n_loops;
         r.reserved[0] = walks_all;    // diagnostics: ray walks executed (speculation + re-searches)
-        r.reserved[1] = walks_first;
-        r.reserved[2] = rewalk_rounds;  // ... warp-level rounds spent on re-searches  // ... of which first-pass walks (= what the sequential algorithm does)
+        r.reserved[1] = walks_first;    // ... of which first-pass walks (= what the sequential algorithm does)
+        r.reserved[2] = dg.rounds;      // verify rounds that had rays to re-search (summed over iterations)
         if (valid_out) {
             r.x[0] = best_x[0];
             r.x[1] = best_x[1];
@@ -474,6 +531,11 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
         for (int k = 0; k < 6; k++) r.cov[k] = (double)pc.acc[3 + k];
         r.error = (double)pc.acc[9];
         r.goodness = (float)pc.acc[10];
+        r.quality = (float)pc.acc[11];
+        r.nvalid = (int)pc.acc[12];
+        r.reserved[3] = (int)pc.acc[13];
+        r.corr_hash = (unsigned)pc.acc[14];
+        r.n_loops = (int)pc.acc[15];
 #endif
         *res = r;
     }

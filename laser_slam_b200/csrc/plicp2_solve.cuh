@@ -200,7 +200,8 @@ __device__ __forceinline__ bool solve4(double A[4][4], double b[4], double x[4])
 
 // S[] = the 14 accumulated sums: M00 M01 M02 M03 M11 M12 M13 M22 M23 M33 g0 g1 g2 g3 (M symmetric: every
 // mirrored pair in gpc.c's d_bigM is the same floating-point expression up to commutation).  Whole-warp call.
-static __device__ __noinline__ bool gpc_solve_warp(const double *S, double x_out[3]) {
+template <class Clock>
+static __device__ __noinline__ bool gpc_solve_warp(const double *S, double x_out[3], Clock *pc) {
     double dM[4][4] = {{S[0], S[1], S[2], S[3]}, {S[1], S[4], S[5], S[6]}, {S[2], S[5], S[7], S[8]}, {S[3], S[6], S[8], S[9]}};
     double bigM[4][4], g[4];
 #pragma unroll
@@ -244,7 +245,9 @@ static __device__ __noinline__ bool gpc_solve_warp(const double *S, double x_out
     double q[5] = {p[0] - (l[0] * l[0]), p[1] - (2 * l[1] * l[0]), p[2] - (l[1] * l[1] + 2 * l[0] * l[2]),
                    -(2 * l[2] * l[1]), -(l[2] * l[2])};
     double lambda;
+    pc->mark(12);
     if (!greatest_real_root4_warp(q, &lambda)) return false;
+    pc->mark(13);
     double A[4][4], b[4], x[4];
 #pragma unroll
     for (int i = 0; i < 4; i++) {
@@ -255,6 +258,7 @@ static __device__ __noinline__ bool gpc_solve_warp(const double *S, double x_out
     A[2][2] += 2 * lambda;
     A[3][3] += 2 * lambda;
     if (!solve4(A, b, x)) return false;
+    pc->mark(14);
     x_out[0] = -x[0];
     x_out[1] = -x[1];
     x_out[2] = atan2(-x[3], -x[2]);

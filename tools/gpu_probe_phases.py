@@ -19,9 +19,12 @@ res = torch.zeros((P, 128), dtype=torch.uint8, device=dev)
 for _ in range(2):
     eng.plicp(scans, ri, si, results=res); eng.sync()
 r = res.cpu().numpy().view(zh.RESULT_DTYPE).reshape(-1)
-ph = np.concatenate([r["x"], r["cov"], r["error"][:, None], r["goodness"][:, None].astype(np.float64)], axis=1)
+ph = np.concatenate([r["x"], r["cov"], r["error"][:, None], r["goodness"][:, None].astype(np.float64), r["quality"][:, None].astype(np.float64),
+                     r["nvalid"][:, None].astype(np.float64), r["reserved"][:, 3:4].astype(np.float64),
+                     r["corr_hash"][:, None].astype(np.float64), r["n_loops"][:, None].astype(np.float64)], axis=1)
 names = ["load", "jump tables", "first-pass walk", "verify + re-search", "kill doubles", "trim keys + select",
-         "kill + GPC sums", "corr hash", "solve (warp 0)", "loop control", "final corr/hash/cov"]
+         "kill + GPC sums", "corr hash", "solve: pose_diff, cos/sin, barrier", "loop control", "final corr/hash/cov",
+         "solve: cross-warp sums", "solve: quartic coefficients", "solve: greatest root", "solve: 4x4 system", "solve: atan2"]
 tot = ph.sum(1)
 print(f"kernel {eng.last_kernel_ms():.2f} ms for {P} pairs; iterations/pair {r['iterations'].mean():.2f}; "
       f"cycles/job {tot.mean():.0f} (thread 0 clock64, includes barrier waits and time-slicing with co-resident CTAs)")

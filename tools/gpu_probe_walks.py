@@ -18,4 +18,4 @@ r = res.cpu().numpy().view(zh.RESULT_DTYPE).reshape(-1)
 w = r["reserved"].astype(np.float64)
 print(f"kernel {eng.last_kernel_ms():.2f} ms for {P} pairs; iterations/pair {r['iterations'].mean():.2f}")
 print(f"walks/pair all {w[:,0].mean():.0f} first-pass {w[:,1].mean():.0f} ratio {w[:,0].sum()/w[:,1].sum():.3f}; "
-      f"re-search warp rounds/pair {w[:,2].mean():.1f} vs first-pass warp rounds {(r['iterations'].mean()*np.ceil(n/32)):.0f}")
+      f"verify rounds with work per iteration {w[:,2].sum()/r['iterations'].sum():.2f}")
