@@ -43,12 +43,21 @@ void plicp_build_hash_matrices(int n, int T, int ch, std::vector<uint32_t> &mat)
     }
 }
 
+size_t plicp_jump_bytes_per_job(int n);
+cudaError_t plicp_jump_launch(const PlicpArgs &a, short *jt, cudaStream_t st);
+
+// a.jt must point at B * plicp_jump_bytes_per_job(n) bytes of scratch: the jump-table kernel fills it, the PL-ICP
+// kernel reads it (same stream).
 cudaError_t plicp_launch(const PlicpArgs &a, int sm_count, cudaStream_t st, int *launched) {
     (void)sm_count;
     int T, C, ch;
     plicp_shape(a.L.n, &T, &C, &ch);
     if (C > 32 || ch != a.hash_chunk) return cudaErrorInvalidValue;
-    cudaError_t e = T == 128 ? plicp_launch_t128(a, st) : T == 256 ? plicp_launch_t256(a, st) : plicp_launch_t512(a, st);
+    if (!a.jt) return cudaErrorInvalidValue;
+    cudaError_t e = plicp_jump_launch(a, const_cast<short *>(a.jt), st);
+    if (e != cudaSuccess) return e;
+    if (launched) *launched += 1;
+    e = T == 128 ? plicp_launch_t128(a, st) : T == 256 ? plicp_launch_t256(a, st) : plicp_launch_t512(a, st);
     if (e == cudaSuccess && launched) *launched += 1;
     return e;
 }

@@ -1,0 +1,146 @@
+// laser_slam_b200/csrc/plicp2_jump.cu -- ld_create_jump_tables(laser_ref) (CSM laser_data.c)
+// as its own kernel, run once per job ahead of the PL-ICP kernel.
+//
+// For every valid ref ray i
+//   up_bigger[i]   = (first j > i that is invalid or has r[j] > r[i]) - i      (n - i when there is none)
+//   up_smaller[i]  = (first j > i that is invalid or has r[j] < r[i]) - i
+//   down_bigger / down_smaller the same towards j < i                          (-1 - i when there is none)
+// A jump can be hundreds of rays long (a wall seen head-on: r falls to the foot of the perpendicular and rises again),
+// so a linear scan per entry is O(n * jump), and CSM's own loop is sequential.  Here every entry is searched
+// independently over a 3-level structure: the rays, the extrema of aligned blocks of 8 rays and of 64 rays.  A search
+// runs to the end of its 8-block, then over 8-blocks to the end of its 64-block, then over 64-blocks, and descends
+// again: at most 7+7+nb64+8+8 probes (47 at 1080 rays), 1-3 for the common short jumps.
+//
+// Why a separate kernel: the searches are chains of dependent shared-memory loads with divergent trip counts.
+// Inside the PL-ICP kernel (3 CTAs = 24 warps per SM, limited by its 75 KB of shared memory) that phase took 10 % of
+// the job; here a CTA needs 5 KB, 64 warps per SM hide the latency, and the tables cost 8 bytes per
+// ray of HBM traffic each way (17 KB per job: nothing against 7.7 TB/s).
+//
+// The comparisons are made on the raw float readings (cm): r = (double)f / 100 is strictly monotone in f, so
+// r[j] <= r[i]  <=>  f[j] <= f[i], and validity is reading_of() of the PL-ICP kernel.  Entries of invalid rays are
+// never read by the walk (it steps by +-1 there) and are set to +-1.
+#include "plicp2_common.cuh"
+
+namespace plicp2 {
+
+// BIG: the search stops at an invalid ray (key -1) or a bigger one; else at an invalid or a smaller one
+template <bool BIG>
+__device__ __forceinline__ bool jt_stop(float k, float v) { return BIG ? (k < 0 || k > v) : (k < v); }
+// block extrema: BIG uses max(valid ? f : +inf), else min(key) (an invalid ray makes it -1 < v)
+template <bool BIG>
+__device__ __forceinline__ bool jt_blk(float m, float v) { return BIG ? (m > v) : (m < v); }
+
+template <bool BIG>
+__device__ __forceinline__ int jt_search_up(const float *key, const float *m8, const float *m64, int n, int nb8,
+                                            int nb64, int j, float v) {
+    while (j < n && (j & 7)) { if (jt_stop<BIG>(key[j], v)) return j; j++; }
+    if (j >= n) return n;
+    int b = j >> 3;
+    bool hit = false;
+    while (b < nb8 && (b & 7)) { if (jt_blk<BIG>(m8[b], v)) { hit = true; break; } b++; }
+    if (!hit) {
+        if (b >= nb8) return n;
+        int c = b >> 3;
+        while (c < nb64 && !jt_blk<BIG>(m64[c], v)) c++;
+        if (c >= nb64) return n;
+        b = c << 3;
+        while (!jt_blk<BIG>(m8[b], v)) b++;  // the block extrema only cover existing rays: stops inside the data
+    }
+    j = b << 3;
+    while (!jt_stop<BIG>(key[j], v)) j++;
+    return j;
+}
+
+template <bool BIG>
+__device__ __forceinline__ int jt_search_down(const float *key, const float *m8, const float *m64, int j, float v) {
+    while (j >= 0 && (j & 7) != 7) { if (jt_stop<BIG>(key[j], v)) return j; j--; }
+    if (j < 0) return -1;
+    int b = j >> 3;
+    bool hit = false;
+    while (b >= 0 && (b & 7) != 7) { if (jt_blk<BIG>(m8[b], v)) { hit = true; break; } b--; }
+    if (!hit) {
+        if (b < 0) return -1;
+        int c = b >> 3;
+        while (c >= 0 && !jt_blk<BIG>(m64[c], v)) c--;
+        if (c < 0) return -1;
+        b = (c << 3) + 7;
+        while (!jt_blk<BIG>(m8[b], v)) b--;
+    }
+    j = (b << 3) + 7;  // every block at or below the start block is complete
+    while (!jt_stop<BIG>(key[j], v)) j--;
+    return j;
+}
+
+constexpr int JT_THREADS = 256;
+
+// jt: [B][4][n] shorts (up_bigger, up_smaller, down_bigger, down_smaller of job b's ref scan)
+__global__ void __launch_bounds__(JT_THREADS) jump_tables_kernel(PlicpArgs a, short *jt) {
+    extern __shared__ float jsm[];
+    const int n = a.L.n, t = threadIdx.x, lane = t & 31;
+    const int nb8 = (n + 7) >> 3, nb64 = (nb8 + 7) >> 3;
+    float *key = jsm;                       // [n] reading in cm, -1 when invalid in the LDP
+    float *hi8 = key + ((n + 31) & ~31);    // [nb8] max(valid ? key : +inf)
+    float *lo8 = hi8 + nb8;                 // [nb8] min(key)
+    float *hi64 = lo8 + nb8, *lo64 = hi64 + nb64;
+    const int job = blockIdx.x;
+    const float *row = a.scans + (size_t)a.ref_idx[job] * n;
+    const int rounds = (n + JT_THREADS - 1) / JT_THREADS;
+    for (int k = 0; k < rounds; k++) {
+        const int i = k * JT_THREADS + t;
+        float hi = 0.f, lo = INFINITY;  // neutral for rays past the end of the scan
+        if (i < n) {
+            int bad = 0;
+            const float f = __ldg(row + i);
+            const float kf = reading_of(f, a.L, a.P, &bad) >= 0 ? f : -1.f;
+            key[i] = kf;
+            hi = kf >= 0 ? kf : INFINITY;
+            lo = kf;
+        }
+#pragma unroll
+        for (int o = 1; o < 8; o <<= 1) {
+            hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+            lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+        }
+        if (i < n && (lane & 7) == 0) { hi8[i >> 3] = hi; lo8[i >> 3] = lo; }
+    }
+    __syncthreads();
+    if (t < nb64) {
+        float hi = 0.f, lo = INFINITY;
+        const int e = (t << 3) + 8 < nb8 ? (t << 3) + 8 : nb8;
+        for (int b = t << 3; b < e; b++) { hi = fmaxf(hi, hi8[b]); lo = fminf(lo, lo8[b]); }
+        hi64[t] = hi;
+        lo64[t] = lo;
+    }
+    __syncthreads();
+    short *out = jt + (size_t)job * 4 * n;
+    for (int i = t; i < n; i += JT_THREADS) {
+        const float v = key[i];
+        int ub = i + 1, us = i + 1, db = i - 1, ds = i - 1;
+        if (v >= 0) {
+            ub = jt_search_up<true>(key, hi8, hi64, n, nb8, nb64, i + 1, v);
+            us = jt_search_up<false>(key, lo8, lo64, n, nb8, nb64, i + 1, v);
+            db = jt_search_down<true>(key, hi8, hi64, i - 1, v);
+            ds = jt_search_down<false>(key, lo8, lo64, i - 1, v);
+        }
+        out[0 * n + i] = (short)(ub - i);
+        out[1 * n + i] = (short)(us - i);
+        out[2 * n + i] = (short)(db - i);
+        out[3 * n + i] = (short)(ds - i);
+    }
+}
+
+}  // namespace plicp2
+
+size_t plicp_jump_bytes_per_job(int n) { return sizeof(short) * 4 * (size_t)n; }
+
+cudaError_t plicp_jump_launch(const PlicpArgs &a, short *jt, cudaStream_t st) {
+    const int n = a.L.n;
+    const int nb8 = (n + 7) >> 3, nb64 = (nb8 + 7) >> 3;
+    const size_t smem = sizeof(float) * (size_t)(((n + 31) & ~31) + 2 * nb8 + 2 * nb64);
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(plicp2::jump_tables_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    plicp2::jump_tables_kernel<<<a.B, plicp2::JT_THREADS, smem, st>>>(a, jt);
+    return cudaGetLastError();
+}

@@ -161,39 +161,28 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
     const float *sens_row = a.scans + (size_t)a.sens_idx[job] * n;
     int bad_field = 0, nvf_ref = 0, nvf_sens = 0;
     unsigned sens = 0;
-    const JumpAux ja = make_jump_aux(l, n);
+    {
+        // jump tables of this job's ref scan, built by jump_tables_kernel (plicp2_jump.cu): 8 bytes per ray
+        const uint2 *src = reinterpret_cast<const uint2 *>(a.jt + (size_t)job * 4 * n);
+        uint2 *dst = PL_SH(uint2, l.jt);
+        for (int q = t; q < n; q += T) dst[q] = __ldg(src + q);
+    }
 #pragma unroll 1
     for (int k = 0; k < C; k++) {
         const int i = k * T + t;
-        double hi = -1.0, lo = INFINITY;  // neutral for the block extrema (rays past the end of the scan)
-        if (i < n) {
-            const double2 cs = a.cs[i];
-            double rr = reading_of(__ldg(ref_row + i), L, P, &bad_field);
-            nvf_ref += (rr != -1.0);
-            const double r2 = rr >= 0 ? rr * rr : -1.0;
-            rr2a[i] = r2;
-            hi = rr >= 0 ? r2 : INFINITY;
-            lo = r2;
-            refp[i] = rr >= 0 ? make_double2(cs.x * rr, cs.y * rr) : make_double2(nan(""), nan(""));
-            double rs = reading_of(__ldg(sens_row + i), L, P, &bad_field);
-            nvf_sens += (rs != -1.0);
-            sensp[i] = rs >= 0 ? make_double2(cs.x * rs, cs.y * rs) : make_double2(nan(""), nan(""));
-            if (rs >= 0) sens |= 1u << k;
-            cj1[i] = -1;
-            cj2[i] = -1;
-            PL_SH(short, l.spec)[i] = -1;
-        }
-        // extrema of the aligned 8-ray blocks for the jump-table searches (T is a multiple of 32: lanes 8g..8g+7
-        // hold rays 8g'..8g'+7)
-#pragma unroll
-        for (int o = 1; o < 8; o <<= 1) {
-            hi = fmax(hi, __shfl_xor_sync(0xffffffffu, hi, o));
-            lo = fmin(lo, __shfl_xor_sync(0xffffffffu, lo, o));
-        }
-        if (i < n && (lane & 7) == 0) {
-            PL_SH(double, ja.hi8)[i >> 3] = hi;
-            PL_SH(double, ja.lo8)[i >> 3] = lo;
-        }
+        if (i >= n) break;
+        const double2 cs = a.cs[i];
+        double rr = reading_of(__ldg(ref_row + i), L, P, &bad_field);
+        nvf_ref += (rr != -1.0);
+        rr2a[i] = rr >= 0 ? rr * rr : -1.0;
+        refp[i] = rr >= 0 ? make_double2(cs.x * rr, cs.y * rr) : make_double2(nan(""), nan(""));
+        double rs = reading_of(__ldg(sens_row + i), L, P, &bad_field);
+        nvf_sens += (rs != -1.0);
+        sensp[i] = rs >= 0 ? make_double2(cs.x * rs, cs.y * rs) : make_double2(nan(""), nan(""));
+        if (rs >= 0) sens |= 1u << k;
+        cj1[i] = -1;
+        cj2[i] = -1;
+        PL_SH(short, l.spec)[i] = -1;
     }
     if (t == 0) {
         for (int k = 0; k < 3; k++) ctl->x[0][k] = a.first_guess ? a.first_guess[3 * (size_t)job + k] : 0.0;
@@ -219,12 +208,7 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
         if (oj1) for (int i = t; i < n; i += T) { oj1[i] = -1; oj2[i] = -1; }
         return;
     }
-    pc.mark(0);
-    jump_aux_level2(ja, t);  // the block sums above were barriers: hi8 / lo8 are complete
-    __syncthreads();
-    build_jump_tables(l, ja, n, t, T);
-    __syncthreads();
-    pc.mark(1);
+    pc.mark(0);  // the block sums above were barriers: the tables are in place
 
     IterCtx it;
     it.min_theta = (double)theta_f(L.fi_min, L.dfi, 0);

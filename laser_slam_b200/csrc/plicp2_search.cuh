@@ -122,114 +122,4 @@ static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int 
     return j1;
 }
 
-// ld_create_jump_tables(laser_ref) (CSM laser_data.c): for every valid ref ray i
-//   up_bigger[i]   = (first j > i that is invalid or has r[j] > r[i]) - i      (n - i when there is none)
-//   up_smaller[i]  = (first j > i that is invalid or has r[j] < r[i]) - i
-//   down_bigger / down_smaller the same towards j < i                          (-1 - i when there is none)
-// A jump can be hundreds of rays long (a wall seen head-on: r falls to the foot of the perpendicular and rises again),
-// so a linear scan per entry is O(n * jump).  Every entry is searched independently here over a 3-level structure:
-// the rays, the extrema of aligned blocks of 8 rays and of 64 rays (JumpAux, filled while the scans are loaded).
-// A search runs to the end of its 8-block, then over 8-blocks to the end of its 64-block, then over 64-blocks, and
-// descends again: at most 7+7+nb64+8+8 steps (47 at 1080 rays), 1-3 for the common short jumps.  Entries of invalid
-// rays are never read by the walk (it steps by +-1 there) and are set to +-1.
-struct JumpAux {
-    unsigned hi8, lo8, hi64, lo64;  // shared-memory byte offsets (inside the d2j area, free until iteration 0)
-    int nb8, nb64;
-};
-
-__device__ __forceinline__ JumpAux make_jump_aux(const Lay &l, int n) {
-    JumpAux a;
-    a.nb8 = (n + 7) >> 3;
-    a.nb64 = (a.nb8 + 7) >> 3;
-    a.hi8 = l.d2j;
-    a.lo8 = a.hi8 + 8u * a.nb8;
-    a.hi64 = a.lo8 + 8u * a.nb8;
-    a.lo64 = a.hi64 + 8u * a.nb64;
-    return a;
-}
-
-// BIG: the search stops at an invalid ray (rr2 = -1) or a bigger one; else at an invalid or a smaller one
-template <bool BIG>
-__device__ __forceinline__ bool jt_stop(double k, double v) { return BIG ? (k < 0 || k > v) : (k < v); }
-// block extrema: BIG uses max(valid ? rr2 : +inf), else min(rr2) (an invalid ray makes it -1 < v)
-template <bool BIG>
-__device__ __forceinline__ bool jt_blk(double m, double v) { return BIG ? (m > v) : (m < v); }
-
-template <bool BIG>
-__device__ __forceinline__ int jt_search_up(const double *rr2a, const double *m8, const double *m64, int n, int nb8,
-                                            int nb64, int i, double v) {
-    int j = i + 1;
-    while (j < n && (j & 7)) { if (jt_stop<BIG>(rr2a[j], v)) return j; j++; }
-    if (j >= n) return n;
-    int b = j >> 3;
-    bool hit = false;
-    while (b < nb8 && (b & 7)) { if (jt_blk<BIG>(m8[b], v)) { hit = true; break; } b++; }
-    if (!hit) {
-        if (b >= nb8) return n;
-        int c = b >> 3;
-        while (c < nb64 && !jt_blk<BIG>(m64[c], v)) c++;
-        if (c >= nb64) return n;
-        b = c << 3;
-        while (!jt_blk<BIG>(m8[b], v)) b++;  // the block extrema only cover existing rays: stops inside the data
-    }
-    j = b << 3;
-    while (!jt_stop<BIG>(rr2a[j], v)) j++;
-    return j;
-}
-
-template <bool BIG>
-__device__ __forceinline__ int jt_search_down(const double *rr2a, const double *m8, const double *m64, int i, double v) {
-    int j = i - 1;
-    while (j >= 0 && (j & 7) != 7) { if (jt_stop<BIG>(rr2a[j], v)) return j; j--; }
-    if (j < 0) return -1;
-    int b = j >> 3;
-    bool hit = false;
-    while (b >= 0 && (b & 7) != 7) { if (jt_blk<BIG>(m8[b], v)) { hit = true; break; } b--; }
-    if (!hit) {
-        if (b < 0) return -1;
-        int c = b >> 3;
-        while (c >= 0 && !jt_blk<BIG>(m64[c], v)) c--;
-        if (c < 0) return -1;
-        b = (c << 3) + 7;
-        while (!jt_blk<BIG>(m8[b], v)) b--;
-    }
-    j = (b << 3) + 7;  // every block at or below the start block is complete
-    while (!jt_stop<BIG>(rr2a[j], v)) j--;
-    return j;
-}
-
-// hi64 / lo64 from hi8 / lo8 (one thread per 64-block); the caller synchronises before and after
-__device__ __forceinline__ void jump_aux_level2(const JumpAux &ja, int t) {
-    if (t < ja.nb64) {
-        const double *hi8 = PL_SH(const double, ja.hi8), *lo8 = PL_SH(const double, ja.lo8);
-        double hi = -1.0, lo = INFINITY;
-        const int e = (t << 3) + 8 < ja.nb8 ? (t << 3) + 8 : ja.nb8;
-        for (int b = t << 3; b < e; b++) { hi = fmax(hi, hi8[b]); lo = fmin(lo, lo8[b]); }
-        PL_SH(double, ja.hi64)[t] = hi;
-        PL_SH(double, ja.lo64)[t] = lo;
-    }
-}
-
-__device__ __forceinline__ void build_jump_tables(const Lay &l, const JumpAux &ja, int n, int t, int nthreads) {
-    short *jt = PL_SH(short, l.jt);
-    const double *rr2a = PL_SH(const double, l.rr2);
-    const double *hi8 = PL_SH(const double, ja.hi8), *lo8 = PL_SH(const double, ja.lo8);
-    const double *hi64 = PL_SH(const double, ja.hi64), *lo64 = PL_SH(const double, ja.lo64);
-#pragma unroll 1
-    for (int i = t; i < n; i += nthreads) {
-        const double v = rr2a[i];  // squares are monotone in r >= 0; invalid = -1
-        int ub = i + 1, us = i + 1, db = i - 1, ds = i - 1;
-        if (v >= 0) {
-            ub = jt_search_up<true>(rr2a, hi8, hi64, n, ja.nb8, ja.nb64, i, v);
-            us = jt_search_up<false>(rr2a, lo8, lo64, n, ja.nb8, ja.nb64, i, v);
-            db = jt_search_down<true>(rr2a, hi8, hi64, i, v);
-            ds = jt_search_down<false>(rr2a, lo8, lo64, i, v);
-        }
-        jt[0 * n + i] = (short)(ub - i);
-        jt[1 * n + i] = (short)(us - i);
-        jt[2 * n + i] = (short)(db - i);
-        jt[3 * n + i] = (short)(ds - i);
-    }
-}
-
 }  // namespace plicp2

@@ -2,6 +2,7 @@
 // Host logic only: argument checks, staging of host buffers, table construction, launches.  No CPU fallback:
 // every compute entry fails with ZHSM_ERR_CUDA when no usable device exists.
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "zhsm_internal.h"
@@ -368,9 +369,25 @@ extern "C" zhsm_status zhsm_plicp_batch(zhsm_handle *h, const float *scans, int 
         if ((flags & ZHSM_WRITEBACK_SCANS) && !(flags & ZHSM_SCANS_ON_DEVICE))
             ZHSM_CUDA_TRY(h, cudaMemcpyAsync(const_cast<float *>(scans), a.scans, scan_bytes, cudaMemcpyDeviceToHost, st));
     }
+    // Jump tables of the jobs' ref scans go through a scratch buffer (8 bytes per ray and job); large batches are
+    // cut into chunks so that the scratch stays bounded (ZHSM_PLICP_CHUNK jobs, default 131072 = 1.1 GB at 1080 beams).
+    int chunk = 131072;
+    if (const char *e = getenv("ZHSM_PLICP_CHUNK")) { int v = atoi(e); if (v >= 1) chunk = v; }
+    if (chunk > B) chunk = B;
+    if ((s = zhsm_stage(h, 15, plicp_jump_bytes_per_job(n) * (size_t)chunk, &p)) != ZHSM_OK) return s;
+    a.jt = (const short *)p;
     ZHSM_CUDA_TRY(h, cudaEventRecord(h->ev0, st));
     int launched = 0;
-    ZHSM_CUDA_TRY(h, plicp_launch(a, h->sm_count, st, &launched));
+    for (int off = 0; off < B; off += chunk) {
+        PlicpArgs c = a;
+        c.B = B - off < chunk ? B - off : chunk;
+        c.ref_idx = a.ref_idx + off;
+        c.sens_idx = a.sens_idx + off;
+        if (a.first_guess) c.first_guess = a.first_guess + 3 * (size_t)off;
+        c.results = a.results + off;
+        if (a.corr_j1) { c.corr_j1 = a.corr_j1 + (size_t)off * n; c.corr_j2 = a.corr_j2 + (size_t)off * n; }
+        ZHSM_CUDA_TRY(h, plicp_launch(c, h->sm_count, st, &launched));
+    }
     h->launches += launched;
     ZHSM_CUDA_TRY(h, cudaEventRecord(h->ev1, st));
     h->ev_valid = true;

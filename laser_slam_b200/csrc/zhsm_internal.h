@@ -49,6 +49,7 @@ struct PlicpArgs {
     zhsm_result *results;    // [B]
     int16_t *corr_j1, *corr_j2; // [B][n] or null
     const double2 *cs;       // [n]
+    const short *jt;         // [B][4][n] jump tables of each job's ref scan (plicp2_jump.cu)
     const uint32_t *hashmat; // [T][32] GF(2) matrices of the parallel ld_corr_hash (plicp2_select.cuh)
     int hash_chunk;          // stream elements hashed per thread (even)
     int B;
@@ -90,6 +91,7 @@ cudaError_t corridor_launch(const float *scans, const unsigned char *bad, const 
 zhsm_status zhsm_stage(zhsm_handle *h, int slot, size_t bytes, void **out);
 
 cudaError_t plicp_launch(const PlicpArgs &a, int sm_count, cudaStream_t st, int *launched);
+size_t plicp_jump_bytes_per_job(int n);
 // CTA shape the PL-ICP kernel uses for n beams: T threads, C rays per thread, hash chunk (even) per thread
 void plicp_shape(int n, int *T, int *C, int *hash_chunk);
 void plicp_build_hash_matrices(int n, int T, int ch, std::vector<uint32_t> &mat);
