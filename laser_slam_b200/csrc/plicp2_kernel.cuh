@@ -214,7 +214,11 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
     it.min_theta = (double)theta_f(L.fi_min, L.dfi, 0);
     it.C1 = (double)n / ((double)theta_f(L.fi_min, L.dfi, n - 1) - it.min_theta);
     WalkCtx wc;
-    wc.refp = l.refp; wc.rr2 = l.rr2; wc.jt = l.jt; wc.n = n; wc.fi_min = L.fi_min; wc.dfi = L.dfi;
+    {
+        const unsigned sb = (unsigned)__cvta_generic_to_shared(smem_raw);
+        wc.refp = sb + l.refp; wc.rr2 = sb + l.rr2; wc.jt = sb + l.jt;
+    }
+    wc.n = n; wc.fi_min = L.fi_min; wc.dfi = L.dfi;
     wc.maxd2 = P.max_correspondence_dist * P.max_correspondence_dist;
     const int max_it = P.max_iterations < ZHSM_MAX_ITER ? P.max_iterations : ZHSM_MAX_ITER;
     const double fail_perc = 0.05;

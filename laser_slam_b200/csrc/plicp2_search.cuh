@@ -44,21 +44,41 @@ __device__ __forceinline__ Ray make_ray(double2 p, double x0, double x1, double 
     return r;
 }
 
-// Geometry a walk needs besides the ray: offsets of the ref tables in shared memory and the beam angles.
+// Geometry a walk needs besides the ray: 32-bit shared-window addresses of the ref tables and the beam angles.
 struct WalkCtx {
-    unsigned refp, rr2, jt;  // shared-memory byte offsets
+    unsigned refp, rr2, jt;  // shared-memory addresses (cvta.to.shared)
     int n;
     float fi_min, dfi;
     double maxd2;
 };
 
+// The tables are constant while the walks run: plain (non-volatile) asm lets the compiler schedule the loads freely,
+// and the 32-bit shared addresses keep the address arithmetic out of the 64-bit generic path.
+__device__ __forceinline__ double lds_f64(unsigned a) {
+    double v;
+    asm("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ double2 lds_f64x2(unsigned a) {
+    double2 v;
+    asm("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ int lds_s16(unsigned a) {
+    short v;
+    asm("ld.shared.s16 %0, [%1];" : "=h"(v) : "r"(a));
+    return (int)v;
+}
+
 // One ray's walk.  Returns j1 (a fully valid correspondence) or -1 and j2 in *j2out.
+// State: up / down = next index to probe in each direction; stopped bit 0 / 1 = that direction has ended.
+// CSM initialises last_dist_up = 0 and last_dist_down = -1; the only use is "last_up < last_down", false for both
+// (0, -1) and (0, 0), so 0 serves for both.
 static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int last_best, int *j2out) {
     const float HALF_PI_F = 1.57079632679489662f;
     const int n = c.n, to = n - 1;
-    const double2 *refp = PL_SH(const double2, c.refp);
-    const double *rr2a = PL_SH(const double, c.rr2);
-    const short *jt = PL_SH(const short, c.jt);
+    const unsigned a_rr2 = c.rr2, a_refp = c.refp;
+    const unsigned a_jt_up = c.jt, a_jt_dn = c.jt + 4u * (unsigned)n, two_n = 2u * (unsigned)n;
     const double wx = r.wx, wy = r.wy, rho2 = r.rho2;
     const int start_cell = r.start_cell;
     int j1 = -1;
@@ -67,55 +87,54 @@ static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int 
     we_start_at = we_start_at > to ? to : we_start_at;
     we_start_at = we_start_at < 0 ? 0 : we_start_at;
     int up = we_start_at + 1, down = we_start_at;
-    double last_up = 0, last_down = -1;
-    bool up_stopped = false, down_stopped = false;
-    while (!(up_stopped && down_stopped)) {
-        const bool now_up = up_stopped ? false : down_stopped ? true : (last_up < last_down);
+    double last_up = 0, last_down = 0;
+    int stopped = 0;
+    const float fi_min = c.fi_min, dfi = c.dfi, phi = r.phi;
+#pragma unroll 1
+    while (stopped != 3) {
+        const bool now_up = (stopped == 2) | ((stopped == 0) & (last_up < last_down));
         const int idx = now_up ? up : down;
-        if (now_up ? (idx > to) : (idx < 0)) {
-            if (now_up) up_stopped = true; else down_stopped = true;
+        const int bit = now_up ? 1 : 2;
+        if ((unsigned)idx > (unsigned)to) {  // ran off either end of the scan
+            stopped |= bit;
             continue;
         }
-        // everything a step may need depends only on idx: issue all shared-memory loads up front so that their
-        // latencies overlap instead of chaining behind the comparisons (the walk is latency-bound)
-        const double rr2 = rr2a[idx];
-        const double2 q = refp[idx];
-        const short *jd = jt + (now_up ? 0 : 2 * n) + idx;
-        const int hop_bigger = jd[0], hop_smaller = jd[n];
-        int step = now_up ? 1 : -1;
-        bool stop = false;
+        const double rr2 = lds_f64(a_rr2 + 8u * idx);
+        const double2 q = lds_f64x2(a_refp + 16u * idx);
+        const int sdir = now_up ? 1 : -1;
+        int nidx = idx + sdir;
         if (rr2 >= 0) {
             const double d = dist2(wx, wy, q.x, q.y);
-            if (now_up) last_up = d; else last_down = d;
-            if (d < best || j1 == -1) { j1 = idx; best = d; }
-            if (now_up ? (idx > start_cell) : (idx < start_cell)) {
-                const float th = theta_f(c.fi_min, c.dfi, idx);
-                const float dth = now_up ? th - r.phi : r.phi - th;
+            last_up = now_up ? d : last_up;
+            last_down = now_up ? last_down : d;
+            const bool better = (d < best) | (j1 == -1);
+            j1 = better ? idx : j1;
+            best = better ? d : best;
+            if ((idx - start_cell) * sdir > 0) {  // beyond the start cell in the walking direction
+                const float dth = theta_f(fi_min, dfi, idx) - phi;  // phi - theta is the exact negation
+                const float sdth = now_up ? dth : -dth;
                 const double cross = wx * q.y - wy * q.x;
-                const bool far = dth > HALF_PI_F;
+                const bool far = sdth > HALF_PI_F;
                 const double lhs = far ? rho2 : cross * cross;
                 const double rhs = far ? best : best * rr2;
-                stop = lhs > rhs;
-                step = rr2 < rho2 ? hop_bigger : hop_smaller;
+                if (lhs > rhs) { stopped |= bit; continue; }
+                nidx = idx + lds_s16((now_up ? a_jt_up : a_jt_dn) + (rr2 < rho2 ? 0u : two_n) + 2u * idx);
             }
         }
-        if (stop) {
-            if (now_up) up_stopped = true; else down_stopped = true;
-        } else {
-            if (now_up) up = idx + step; else down = idx + step;
-        }
+        up = now_up ? nidx : up;
+        down = now_up ? down : nidx;
     }
     if (j1 == -1 || best > c.maxd2) return -1;
     if (j1 == 0 || j1 == n - 1) return -1;
     int j2up = -1, j2down = -1;
-    for (int j = j1 + 1; j < n; j++) if (rr2a[j] >= 0) { j2up = j; break; }
-    for (int j = j1 - 1; j >= 0; j--) if (rr2a[j] >= 0) { j2down = j; break; }
+    for (int j = j1 + 1; j < n; j++) if (lds_f64(a_rr2 + 8u * j) >= 0) { j2up = j; break; }
+    for (int j = j1 - 1; j >= 0; j--) if (lds_f64(a_rr2 + 8u * j) >= 0) { j2down = j; break; }
     if (j2up == -1 && j2down == -1) return -1;
     int j2;
     if (j2up == -1) j2 = j2down;
     else if (j2down == -1) j2 = j2up;
     else {
-        const double2 qu = refp[j2up], qd = refp[j2down];
+        const double2 qu = lds_f64x2(a_refp + 16u * j2up), qd = lds_f64x2(a_refp + 16u * j2down);
         j2 = dist2(wx, wy, qu.x, qu.y) < dist2(wx, wy, qd.x, qd.y) ? j2up : j2down;
     }
     *j2out = j2;
