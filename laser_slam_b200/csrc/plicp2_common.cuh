@@ -46,7 +46,7 @@ struct Lay {
     unsigned cj1;    // short[n] current correspondences (-1 none): fixpoint exchange, hash stream, output
     unsigned cj2;    // short[n]
     unsigned spec;   // short[n] last_best each ray was (or will be) searched with
-    unsigned jt;     // short[4][n] up_bigger, up_smaller, down_bigger, down_smaller
+    unsigned jt;     // short[2][n][2] pairs (up_bigger, up_smaller)[n], (down_bigger, down_smaller)[n]
     unsigned total;
 };
 

@@ -73,7 +73,8 @@ __device__ __forceinline__ int jt_search_down(const float *key, const float *m8,
 
 constexpr int JT_THREADS = 256;
 
-// jt: [B][4][n] shorts (up_bigger, up_smaller, down_bigger, down_smaller of job b's ref scan)
+// jt: [B][2][n][2] shorts: per job the pairs (up_bigger, up_smaller)[n] then (down_bigger, down_smaller)[n] of its
+// ref scan -- the walk fetches both jumps of a direction with one 32-bit load
 __global__ void __launch_bounds__(JT_THREADS) jump_tables_kernel(PlicpArgs a, short *jt) {
     extern __shared__ float jsm[];
     const int n = a.L.n, t = threadIdx.x, lane = t & 31;
@@ -112,7 +113,7 @@ __global__ void __launch_bounds__(JT_THREADS) jump_tables_kernel(PlicpArgs a, sh
         lo64[t] = lo;
     }
     __syncthreads();
-    short *out = jt + (size_t)job * 4 * n;
+    short2 *out2 = reinterpret_cast<short2 *>(jt + (size_t)job * 4 * n);
     for (int i = t; i < n; i += JT_THREADS) {
         const float v = key[i];
         int ub = i + 1, us = i + 1, db = i - 1, ds = i - 1;
@@ -122,10 +123,8 @@ __global__ void __launch_bounds__(JT_THREADS) jump_tables_kernel(PlicpArgs a, sh
             db = jt_search_down<true>(key, hi8, hi64, i - 1, v);
             ds = jt_search_down<false>(key, lo8, lo64, i - 1, v);
         }
-        out[0 * n + i] = (short)(ub - i);
-        out[1 * n + i] = (short)(us - i);
-        out[2 * n + i] = (short)(db - i);
-        out[3 * n + i] = (short)(ds - i);
+        out2[i] = make_short2((short)(ub - i), (short)(us - i));
+        out2[n + i] = make_short2((short)(db - i), (short)(ds - i));
     }
 }
 

@@ -64,10 +64,12 @@ __device__ __forceinline__ double2 lds_f64x2(unsigned a) {
     asm("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(a));
     return v;
 }
-__device__ __forceinline__ int lds_s16(unsigned a) {
-    short v;
-    asm("ld.shared.s16 %0, [%1];" : "=h"(v) : "r"(a));
-    return (int)v;
+// (ptxas sinks this load to its conditional use whatever the source order; ld.volatile keeps it early but
+// serialises the step -- measured 27 % slower)
+__device__ __forceinline__ int lds_b32(unsigned a) {
+    int v;
+    asm("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(a));
+    return v;
 }
 
 // One ray's walk.  Returns j1 (a fully valid correspondence) or -1 and j2 in *j2out.
@@ -78,11 +80,11 @@ static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int 
     const float HALF_PI_F = 1.57079632679489662f;
     const int n = c.n, to = n - 1;
     const unsigned a_rr2 = c.rr2, a_refp = c.refp;
-    const unsigned a_jt_up = c.jt, a_jt_dn = c.jt + 4u * (unsigned)n, two_n = 2u * (unsigned)n;
+    const unsigned a_jt_up = c.jt, a_jt_dn = c.jt + 4u * (unsigned)n;  // [2][n] pairs (bigger, smaller)
     const double wx = r.wx, wy = r.wy, rho2 = r.rho2;
     const int start_cell = r.start_cell;
     int j1 = -1;
-    double best = 42;
+    double best = INFINITY;  // CSM: best_dist = 42 with "j1 == -1 ||" in front of every comparison: the same
     int we_start_at = (last_best == -1) ? start_cell : last_best + 1;
     we_start_at = we_start_at > to ? to : we_start_at;
     we_start_at = we_start_at < 0 ? 0 : we_start_at;
@@ -101,24 +103,33 @@ static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int 
         }
         const double rr2 = lds_f64(a_rr2 + 8u * idx);
         const double2 q = lds_f64x2(a_refp + 16u * idx);
+        const int hops = lds_b32((now_up ? a_jt_up : a_jt_dn) + 4u * idx);  // both jumps of this direction
         const int sdir = now_up ? 1 : -1;
         int nidx = idx + sdir;
         if (rr2 >= 0) {
             const double d = dist2(wx, wy, q.x, q.y);
             last_up = now_up ? d : last_up;
             last_down = now_up ? last_down : d;
-            const bool better = (d < best) | (j1 == -1);
+            const bool better = d < best;
             j1 = better ? idx : j1;
             best = better ? d : best;
             if ((idx - start_cell) * sdir > 0) {  // beyond the start cell in the walking direction
                 const float dth = theta_f(fi_min, dfi, idx) - phi;  // phi - theta is the exact negation
                 const float sdth = now_up ? dth : -dth;
                 const double cross = wx * q.y - wy * q.x;
-                const bool far = sdth > HALF_PI_F;
-                const double lhs = far ? rho2 : cross * cross;
-                const double rhs = far ? best : best * rr2;
-                if (lhs > rhs) { stopped |= bit; continue; }
-                nidx = idx + lds_s16((now_up ? a_jt_up : a_jt_dn) + (rr2 < rho2 ? 0u : two_n) + 2u * idx);
+                // stop = dth > pi/2 ? rho2 > best : cross^2 > best * rr2, kept in predicate registers
+                int stop;
+                asm("{ .reg .pred pf, pa, pb;\n\t"
+                    "setp.gt.f32 pf, %1, %2;\n\t"
+                    "setp.gt.and.f64 pa, %3, %4, pf;\n\t"
+                    "not.pred pf, pf;\n\t"
+                    "setp.gt.and.f64 pb, %5, %6, pf;\n\t"
+                    "or.pred pa, pa, pb;\n\t"
+                    "selp.s32 %0, 1, 0, pa; }"
+                    : "=r"(stop)
+                    : "f"(sdth), "f"(HALF_PI_F), "d"(rho2), "d"(best), "d"(cross * cross), "d"(best * rr2));
+                if (stop) { stopped |= bit; continue; }
+                nidx = idx + (rr2 < rho2 ? (int)(short)hops : hops >> 16);
             }
         }
         up = now_up ? nidx : up;

@@ -49,7 +49,7 @@ struct PlicpArgs {
     zhsm_result *results;    // [B]
     int16_t *corr_j1, *corr_j2; // [B][n] or null
     const double2 *cs;       // [n]
-    const short *jt;         // [B][4][n] jump tables of each job's ref scan (plicp2_jump.cu)
+    const short *jt;         // [B][2][n][2] jump tables of each job's ref scan (plicp2_jump.cu)
     const uint32_t *hashmat; // [T][32] GF(2) matrices of the parallel ld_corr_hash (plicp2_select.cuh)
     int hash_chunk;          // stream elements hashed per thread (even)
     int B;
