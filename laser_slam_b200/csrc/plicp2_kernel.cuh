@@ -14,8 +14,8 @@ namespace plicp2 {
 // x/cov/error/goodness/quality in the result record, see tools/gpu_probe_phases.py).
 struct PhaseClock {
 #ifdef PLICP_PHASE_TIMING
-    long long last, acc[16];
-    __device__ __forceinline__ void start() { for (int k = 0; k < 16; k++) acc[k] = 0; last = clock64(); }
+    long long last, acc[20];
+    __device__ __forceinline__ void start() { for (int k = 0; k < 20; k++) acc[k] = 0; last = clock64(); }
     __device__ __forceinline__ void mark(int k) { const long long c = clock64(); acc[k] += c - last; last = c; }
 #else
     __device__ __forceinline__ void start() {}
@@ -56,20 +56,43 @@ __device__ __forceinline__ bool search_ray(const Lay &l, const WalkCtx &w, const
 // sens: bit k = ray k*T+t exists and is valid; returns the mask of those rays holding a correspondence.
 template <int T>
 __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const WalkCtx &w, const IterCtx &it, int C,
-                                                         unsigned sens, WalkDiag &dg, PhaseClock &pc) {
+                                                         unsigned sens, bool chunked, WalkDiag &dg, PhaseClock &pc) {
     constexpr int NW = T / 32;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int n = w.n;
     const unsigned lane_lt = (1u << lane) - 1u;
     Ctl *ctl = PL_SH(Ctl, l.ctl);
     if (t == 0) ctl->qn[0] = 0;
+    if (!chunked) {
 #pragma unroll 1
-    for (int k = 0; k < C; k++)
-        if (sens >> k & 1u) {
+        for (int k = 0; k < C; k++)
+            if (sens >> k & 1u) {
+                dg.walks++;
+                dg.first++;
+                search_ray(l, w, it, k * T + t);
+            }
+    } else {
+        // thread t walks the rays [t*C, (t+1)*C) in order and hands last_best from one to the next: only the first
+        // ray of a chunk is speculated
+        const double2 *sensp = PL_SH(const double2, l.sensp);
+        short *specw = PL_SH(short, l.spec);
+        const short *cj1r = PL_SH(const short, l.cj1);
+        int lb = 0;
+        bool have = false;
+#pragma unroll 1
+        for (int q = 0; q < C; q++) {
+            const int i = t * C + q;
+            if (i >= n) break;
+            if (sensp[i].x != sensp[i].x) continue;  // invalid sens ray: no walk, last_best unchanged
+            if (have) specw[i] = (short)lb;
             dg.walks++;
             dg.first++;
-            search_ray(l, w, it, k * T + t);
+            search_ray(l, w, it, i);
+            const int c1 = cj1r[i];
+            lb = c1 >= 0 ? c1 : (int)specw[i];
+            have = true;
         }
+    }
     __syncthreads();
     pc.mark(2);
     short *cj1 = PL_SH(short, l.cj1);
@@ -138,7 +161,7 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
 }
 
 template <int T>
-__global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2_kernel(PlicpArgs a) {
+__global__ void __launch_bounds__(T, (T <= 256 ? 3 : 1)) plicp2_kernel(PlicpArgs a) {
     constexpr int NW = T / 32;
     const int n = a.L.n;
     const int C = (n + T - 1) / T;
@@ -238,7 +261,7 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
             it.cs = ctl->cs[par];
             it.sn = ctl->sn[par];
             if (t == 0) ctl->hash_acc[iteration & 1] = 0;
-            valid = find_correspondences<T>(l, wc, it, C, sens, dg, pc);
+            valid = find_correspondences<T>(l, wc, it, C, sens, iteration < a.chunk_iters, dg, pc);
             if (P.outliers_remove_doubles) {
                 for (int j = t; j < n; j += T) d2j[j] = BIG;  // the search used this area as its queue
                 __syncthreads();
@@ -288,6 +311,7 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
                 const double2 q1 = refp[cj1[i]], q2 = refp[cj2[i]];
                 d2j[i] = (unsigned long long)__double_as_longlong(dist_to_segment(q1.x, q1.y, q2.x, q2.y, wx, wy));
             }
+            pc.mark(16);
             int order = (int)floor(kcnt * P.outliers_maxPerc);
             order = order < kcnt - 1 ? order : kcnt - 1;
             order = order > 0 ? order : 0;
@@ -295,7 +319,7 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
             order2 = order2 < kcnt - 1 ? order2 : kcnt - 1;
             order2 = order2 > 0 ? order2 : 0;
             double lim1, d_o2;
-            select2<T>(l, C, valid, order, order2, lim1, d_o2);
+            select2<T>(l, C, valid, order, order2, lim1, d_o2, pc);
             pc.mark(5);
             const double lim2 = P.outliers_adaptive_mult * d_o2;
             const double error_limit = lim1 < lim2 ? lim1 : lim2;
@@ -471,7 +495,7 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
         it.cs = ctl->cs[0];
         it.sn = ctl->sn[0];
         // "recompute correspondences in case of restarts" (icp.c): world coords at best x + tricks, no outlier pass
-        if (v_restarted) valid = find_correspondences<T>(l, wc, it, C, sens, dg, pc);
+        if (v_restarted) valid = find_correspondences<T>(l, wc, it, C, sens, a.chunk_iters > 0, dg, pc);
     }
     if (t == 0) ctl->hash_acc[0] = 0;
 #pragma unroll 1
@@ -515,6 +539,7 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
         }
 #ifdef PLICP_PHASE_TIMING
         pc.mark(10);
+        pc.acc[5] += pc.acc[19];
         for (int k = 0; k < 3; k++) r.x[k] = (double)pc.acc[k];
         for (int k = 0; k < 6; k++) r.cov[k] = (double)pc.acc[3 + k];
         r.error = (double)pc.acc[9];
@@ -524,6 +549,7 @@ __global__ void __launch_bounds__(T, (T <= 128 ? 3 : (T <= 256 ? 3 : 1))) plicp2
         r.reserved[3] = (int)pc.acc[13];
         r.corr_hash = (unsigned)pc.acc[14];
         r.n_loops = (int)pc.acc[15];
+        for (int k = 0; k < 3; k++) r.reserved[k] = (int)pc.acc[16 + k];
 #endif
         *res = r;
     }

@@ -24,9 +24,9 @@ __device__ __forceinline__ int block_sum(int v, int *ired, int slot) {
 // warp redundantly locates the buckets (no second barrier).  A bucket holding a single key ends that rank early
 // (the key's owner index is remembered next to the histogram); three rotating histogram sets make the zeroing of
 // the next set race-free.
-template <int T>
+template <int T, class Clock>
 __device__ __forceinline__ void select2(const Lay &l, int C, unsigned valid, int rank0, int rank1, double &v0,
-                                        double &v1) {
+                                        double &v1, Clock &pc) {
     const int t = threadIdx.x, lane = t & 31;
     const unsigned long long *keyS = PL_SH(const unsigned long long, l.d2j);
     int *hist_all = PL_SH(int, l.hist);
@@ -56,6 +56,7 @@ __device__ __forceinline__ void select2(const Lay &l, int C, unsigned valid, int
             if (m1) cand[256 + digit] = (short)i;
         }
         __syncthreads();
+        pc.mark(18);
         int loc[8];
 #pragma unroll
         for (int q = 0; q < 8; q++) loc[q] = hist[lane * 8 + q];
@@ -98,6 +99,7 @@ __device__ __forceinline__ void select2(const Lay &l, int C, unsigned valid, int
                                    : __longlong_as_double((long long)keyS[cand[256 * r + digit]]);
             }
         }
+        pc.mark(19);
         if (done[0] && done[1]) break;
     }
     v0 = val[0];

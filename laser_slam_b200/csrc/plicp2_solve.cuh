@@ -39,6 +39,15 @@ __device__ __forceinline__ void section_rounds(const double *c, double &lo, doub
     }
 }
 
+// 1/x to ~1e-9 relative (hardware seed + one Newton step): the root iteration below only needs a good step, its fixed
+// point does not depend on how the quotient was rounded
+__device__ __forceinline__ double rcp_fast(double x) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    const double e = 1.0 - x * r;
+    return r + r * e;
+}
+
 template <int DEG>
 __device__ __forceinline__ double root_monotone_warp(const double *c, double lo, double hi, double flo) {
     const bool lo_neg = flo < 0;
@@ -54,7 +63,7 @@ __device__ __forceinline__ double root_monotone_warp(const double *c, double lo,
         if (fx == 0) { converged = true; break; }
         const double dfx = poly_eval(dc, DEG - 1, x);
         if (dfx == 0) break;
-        const double xn = x - fx / dfx;
+        const double xn = x - fx * rcp_fast(dfx);
         if (!(xn >= lo && xn <= hi)) break;
         const double step = fabs(xn - x);
         x = xn;
@@ -112,8 +121,10 @@ static __device__ __noinline__ bool greatest_real_root4_warp(const double *a, do
     for (int i = 1; i <= 4; i++) d3[i - 1] = a[i] * i;
 #pragma unroll
     for (int i = 1; i <= 3; i++) d2[i - 1] = d3[i] * i;
-    // monotone pieces of the cubic: [-B3, roots of the quadratic d2 (closed form, ascending), B3]
-    const double B3 = root_bound(d3, 3);
+    // Every root of the derivative lies in the convex hull of the quartic's roots (Gauss-Lucas), so the quartic's
+    // root bound also bounds the cubic's.  Monotone pieces of the cubic: [-B, roots of the quadratic d2, B]
+    const double B4 = root_bound(a, 4);
+    const double B3 = B4;
     double pts[4];
     int np = 0;
     pts[np++] = -B3;
@@ -136,10 +147,25 @@ static __device__ __noinline__ bool greatest_real_root4_warp(const double *a, do
     int piece = np - 2;
     double last = 0;
     bool have_last = false;
-    const double B4 = root_bound(a, 4);
     double hi = B4, fhi = poly_eval(a, 4, hi);
     if (fhi == 0) { *root = hi; return true; }
     if (isnan(fhi)) return false;
+    // Usual case, without refining the critical point: the right-most piece of the cubic changes sign, a few section
+    // rounds bracket that greatest critical point from above by cu, and the quartic changes sign on [cu, B] -- it is
+    // monotone there, so that sign change is the greatest root.  Anything else takes the general path below.
+    {
+        const double ca = pts[np - 2], cb = pts[np - 1];
+        const double fa = poly_eval(d3, 3, ca), fb = poly_eval(d3, 3, cb);
+        if (fa != 0 && fb != 0 && ((fa < 0) != (fb < 0))) {
+            double cl = ca, cu = cb;
+            section_rounds<3>(d3, cl, cu, fa < 0, 4);
+            const double fcu = poly_eval(a, 4, cu);
+            if (cu < hi && fcu != 0 && ((fcu < 0) != (fhi < 0))) {
+                *root = root_monotone_warp<4>(a, cu, hi, fcu);
+                return true;
+            }
+        }
+    }
 #pragma unroll 1
     for (int guard = 0; guard < 8; guard++) {
         double c;

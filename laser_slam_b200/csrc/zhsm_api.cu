@@ -314,6 +314,8 @@ extern "C" zhsm_status zhsm_plicp_batch(zhsm_handle *h, const float *scans, int 
     a.cs = h->d_cs;
     a.hashmat = h->d_hashmat;
     a.hash_chunk = h->hash_chunk;
+    a.chunk_iters = 2;
+    if (const char *e = getenv("ZHSM_PLICP_CHUNK_ITERS")) a.chunk_iters = atoi(e);  // tuning only
 
     // ld_valid_fields' per-scan-geometry checks (laser_data.c): nrays, fov, theta[] consistent by construction
     {

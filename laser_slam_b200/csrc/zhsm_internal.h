@@ -52,6 +52,7 @@ struct PlicpArgs {
     const short *jt;         // [B][2][n][2] jump tables of each job's ref scan (plicp2_jump.cu)
     const uint32_t *hashmat; // [T][32] GF(2) matrices of the parallel ld_corr_hash (plicp2_select.cuh)
     int hash_chunk;          // stream elements hashed per thread (even)
+    int chunk_iters;         // first iterations of an icp_loop searched in chunk order (find_correspondences)
     int B;
     LaserDev L;
     zhsm_plicp_params P;

@@ -21,10 +21,12 @@ for _ in range(2):
 r = res.cpu().numpy().view(zh.RESULT_DTYPE).reshape(-1)
 ph = np.concatenate([r["x"], r["cov"], r["error"][:, None], r["goodness"][:, None].astype(np.float64), r["quality"][:, None].astype(np.float64),
                      r["nvalid"][:, None].astype(np.float64), r["reserved"][:, 3:4].astype(np.float64),
-                     r["corr_hash"][:, None].astype(np.float64), r["n_loops"][:, None].astype(np.float64)], axis=1)
-names = ["load", "jump tables", "first-pass walk", "verify + re-search", "kill doubles", "trim keys + select",
+                     r["corr_hash"][:, None].astype(np.float64), r["n_loops"][:, None].astype(np.float64),
+                     r["reserved"][:, 0:3].astype(np.float64)], axis=1)
+names = ["load", "jump tables", "first-pass walk", "verify + re-search", "kill doubles", "select: bucket search (all passes)",
          "kill + GPC sums", "corr hash", "solve: pose_diff, cos/sin, barrier", "loop control", "final corr/hash/cov",
-         "solve: cross-warp sums", "solve: quartic coefficients", "solve: greatest root", "solve: 4x4 system", "solve: atan2"]
+         "solve: cross-warp sums", "solve: quartic coefficients", "solve: greatest root", "solve: 4x4 system", "solve: atan2",
+         "trim: keys (dist_to_segment)", "(unused)", "select: histogram passes + barrier"]
 tot = ph.sum(1)
 print(f"kernel {eng.last_kernel_ms():.2f} ms for {P} pairs; iterations/pair {r['iterations'].mean():.2f}; "
       f"cycles/job {tot.mean():.0f} (thread 0 clock64, includes barrier waits and time-slicing with co-resident CTAs)")
