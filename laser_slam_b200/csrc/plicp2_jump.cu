@@ -17,20 +17,27 @@
 // ray of HBM traffic each way (17 KB per job: nothing against 7.7 TB/s).
 //
 // The comparisons are made on the raw float readings (cm): r = (double)f / 100 is strictly monotone in f, so
-// r[j] <= r[i]  <=>  f[j] <= f[i], and validity is reading_of() of the PL-ICP kernel.  Entries of invalid rays are
-// never read by the walk (it steps by +-1 there) and are set to +-1.
+// r[j] <= r[i]  <=>  f[j] <= f[i], and validity is reading_of() of the PL-ICP kernel.
+//
+// Entries of INVALID rays: CSM never reads them -- its walk skips an invalid ref ray with ++up / --down and nothing
+// else changes, so the next trip takes the same direction again until a valid ray or the end of the scan.  Both
+// entries of an invalid ray therefore hold the length of that whole skip (to the next valid ray; n - i / -1 - i when
+// there is none), and the kernel's walk crosses a run of invalid rays in one probe.
 #include "plicp2_common.cuh"
 
 namespace plicp2 {
 
-// BIG: the search stops at an invalid ray (key -1) or a bigger one; else at an invalid or a smaller one
-template <bool BIG>
-__device__ __forceinline__ bool jt_stop(float k, float v) { return BIG ? (k < 0 || k > v) : (k < v); }
-// block extrema: BIG uses max(valid ? f : +inf), else min(key) (an invalid ray makes it -1 < v)
-template <bool BIG>
-__device__ __forceinline__ bool jt_blk(float m, float v) { return BIG ? (m > v) : (m < v); }
+// MODE 0 (bigger): the search stops at an invalid ray (key -1) or a bigger one; MODE 1 (smaller): at an invalid or a
+// smaller one; MODE 2 (next valid, for invalid rays): at any valid ray
+template <int MODE>
+__device__ __forceinline__ bool jt_stop(float k, float v) {
+    return MODE == 0 ? (k < 0 || k > v) : MODE == 1 ? (k < v) : (k >= 0);
+}
+// block extrema: MODE 0 uses max(valid ? f : +inf), MODE 1 min(key) (an invalid ray makes it -1 < v), MODE 2 max(key)
+template <int MODE>
+__device__ __forceinline__ bool jt_blk(float m, float v) { return MODE == 0 ? (m > v) : MODE == 1 ? (m < v) : (m >= 0); }
 
-template <bool BIG>
+template <int BIG>
 __device__ __forceinline__ int jt_search_up(const float *key, const float *m8, const float *m64, int n, int nb8,
                                             int nb64, int j, float v) {
     while (j < n && (j & 7)) { if (jt_stop<BIG>(key[j], v)) return j; j++; }
@@ -51,7 +58,7 @@ __device__ __forceinline__ int jt_search_up(const float *key, const float *m8, c
     return j;
 }
 
-template <bool BIG>
+template <int BIG>
 __device__ __forceinline__ int jt_search_down(const float *key, const float *m8, const float *m64, int j, float v) {
     while (j >= 0 && (j & 7) != 7) { if (jt_stop<BIG>(key[j], v)) return j; j--; }
     if (j < 0) return -1;
@@ -83,12 +90,13 @@ __global__ void __launch_bounds__(JT_THREADS) jump_tables_kernel(PlicpArgs a, sh
     float *hi8 = key + ((n + 31) & ~31);    // [nb8] max(valid ? key : +inf)
     float *lo8 = hi8 + nb8;                 // [nb8] min(key)
     float *hi64 = lo8 + nb8, *lo64 = hi64 + nb64;
+    float *any8 = lo64 + nb64, *any64 = any8 + nb8;  // max(key): >= 0 when the block holds a valid ray
     const int job = blockIdx.x;
     const float *row = a.scans + (size_t)a.ref_idx[job] * n;
     const int rounds = (n + JT_THREADS - 1) / JT_THREADS;
     for (int k = 0; k < rounds; k++) {
         const int i = k * JT_THREADS + t;
-        float hi = 0.f, lo = INFINITY;  // neutral for rays past the end of the scan
+        float hi = 0.f, lo = INFINITY, any = -1.f;  // neutral for rays past the end of the scan
         if (i < n) {
             int bad = 0;
             const float f = __ldg(row + i);
@@ -96,32 +104,38 @@ __global__ void __launch_bounds__(JT_THREADS) jump_tables_kernel(PlicpArgs a, sh
             key[i] = kf;
             hi = kf >= 0 ? kf : INFINITY;
             lo = kf;
+            any = kf;
         }
 #pragma unroll
         for (int o = 1; o < 8; o <<= 1) {
             hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
             lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+            any = fmaxf(any, __shfl_xor_sync(0xffffffffu, any, o));
         }
-        if (i < n && (lane & 7) == 0) { hi8[i >> 3] = hi; lo8[i >> 3] = lo; }
+        if (i < n && (lane & 7) == 0) { hi8[i >> 3] = hi; lo8[i >> 3] = lo; any8[i >> 3] = any; }
     }
     __syncthreads();
     if (t < nb64) {
-        float hi = 0.f, lo = INFINITY;
+        float hi = 0.f, lo = INFINITY, any = -1.f;
         const int e = (t << 3) + 8 < nb8 ? (t << 3) + 8 : nb8;
-        for (int b = t << 3; b < e; b++) { hi = fmaxf(hi, hi8[b]); lo = fminf(lo, lo8[b]); }
+        for (int b = t << 3; b < e; b++) { hi = fmaxf(hi, hi8[b]); lo = fminf(lo, lo8[b]); any = fmaxf(any, any8[b]); }
         hi64[t] = hi;
         lo64[t] = lo;
+        any64[t] = any;
     }
     __syncthreads();
     short2 *out2 = reinterpret_cast<short2 *>(jt + (size_t)job * 4 * n);
     for (int i = t; i < n; i += JT_THREADS) {
         const float v = key[i];
-        int ub = i + 1, us = i + 1, db = i - 1, ds = i - 1;
+        int ub, us, db, ds;
         if (v >= 0) {
-            ub = jt_search_up<true>(key, hi8, hi64, n, nb8, nb64, i + 1, v);
-            us = jt_search_up<false>(key, lo8, lo64, n, nb8, nb64, i + 1, v);
-            db = jt_search_down<true>(key, hi8, hi64, i - 1, v);
-            ds = jt_search_down<false>(key, lo8, lo64, i - 1, v);
+            ub = jt_search_up<0>(key, hi8, hi64, n, nb8, nb64, i + 1, v);
+            us = jt_search_up<1>(key, lo8, lo64, n, nb8, nb64, i + 1, v);
+            db = jt_search_down<0>(key, hi8, hi64, i - 1, v);
+            ds = jt_search_down<1>(key, lo8, lo64, i - 1, v);
+        } else {
+            ub = us = jt_search_up<2>(key, any8, any64, n, nb8, nb64, i + 1, v);
+            db = ds = jt_search_down<2>(key, any8, any64, i - 1, v);
         }
         out2[i] = make_short2((short)(ub - i), (short)(us - i));
         out2[n + i] = make_short2((short)(db - i), (short)(ds - i));
@@ -135,7 +149,7 @@ size_t plicp_jump_bytes_per_job(int n) { return sizeof(short) * 4 * (size_t)n; }
 cudaError_t plicp_jump_launch(const PlicpArgs &a, short *jt, cudaStream_t st) {
     const int n = a.L.n;
     const int nb8 = (n + 7) >> 3, nb64 = (nb8 + 7) >> 3;
-    const size_t smem = sizeof(float) * (size_t)(((n + 31) & ~31) + 2 * nb8 + 2 * nb64);
+    const size_t smem = sizeof(float) * (size_t)(((n + 31) & ~31) + 3 * nb8 + 3 * nb64);
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(plicp2::jump_tables_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;

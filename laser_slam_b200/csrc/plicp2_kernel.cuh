@@ -35,11 +35,32 @@ struct IterCtx {
     double min_theta, C1;
 };
 
+#ifdef PLICP_WALK_STATS
+// tuning build: per-thread walk statistics (trips, trips of walks > 32, count, trips of walks > 256, count, max)
+#define g_stats st_
+#define STATS_PARAM , int *st_
+#define STATS_ARG , st_
+#else
+#define STATS_PARAM
+#define STATS_ARG
+#endif
+
 // search sens ray i with its speculated last_best; returns true when it got a correspondence
-__device__ __forceinline__ bool search_ray(const Lay &l, const WalkCtx &w, const IterCtx &it, int i) {
+__device__ __forceinline__ bool search_ray(const Lay &l, const WalkCtx &w, const IterCtx &it, int i STATS_PARAM) {
     const Ray ray = make_ray(PL_SH(const double2, l.sensp)[i], it.x0, it.x1, it.cs, it.sn, it.min_theta, it.C1);
     int j2 = -1;
+#ifdef PLICP_WALK_STATS
+    int trips = 0;
+    const int j1 = tricks_one(w, ray, (int)PL_SH(const short, l.spec)[i], &j2, &trips);
+    g_stats[0] += trips;
+    g_stats[1] += trips > 32 ? trips : 0;
+    g_stats[2] += trips > 32;
+    g_stats[3] += trips > 256 ? trips : 0;
+    g_stats[4] += trips > 256;
+    g_stats[5] = trips > g_stats[5] ? trips : g_stats[5];
+#else
     const int j1 = tricks_one(w, ray, (int)PL_SH(const short, l.spec)[i], &j2);
+#endif
     PL_SH(short, l.cj1)[i] = (short)j1;
     PL_SH(short, l.cj2)[i] = (short)(j1 >= 0 ? j2 : -1);
     return j1 >= 0;
@@ -56,7 +77,7 @@ __device__ __forceinline__ bool search_ray(const Lay &l, const WalkCtx &w, const
 // sens: bit k = ray k*T+t exists and is valid; returns the mask of those rays holding a correspondence.
 template <int T>
 __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const WalkCtx &w, const IterCtx &it, int C,
-                                                         unsigned sens, bool chunked, WalkDiag &dg, PhaseClock &pc) {
+                                                         unsigned sens, bool chunked, WalkDiag &dg, PhaseClock &pc STATS_PARAM) {
     constexpr int NW = T / 32;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int n = w.n;
@@ -69,7 +90,7 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
             if (sens >> k & 1u) {
                 dg.walks++;
                 dg.first++;
-                search_ray(l, w, it, k * T + t);
+                search_ray(l, w, it, k * T + t STATS_ARG);
             }
     } else {
         // thread t walks the rays [t*C, (t+1)*C) in order and hands last_best from one to the next: only the first
@@ -87,7 +108,7 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
             if (have) specw[i] = (short)lb;
             dg.walks++;
             dg.first++;
-            search_ray(l, w, it, i);
+            search_ray(l, w, it, i STATS_ARG);
             const int c1 = cj1r[i];
             lb = c1 >= 0 ? c1 : (int)specw[i];
             have = true;
@@ -147,7 +168,7 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
             const int i = (int)queue[e];
             const int before = cj1[i];
             dg.walks++;
-            search_ray(l, w, it, i);
+            search_ray(l, w, it, i STATS_ARG);
             changed |= (int)cj1[i] != before;
         }
         if (!__syncthreads_or(changed)) break;  // last_best of every ray is what it was walked with
@@ -252,6 +273,10 @@ __global__ void __launch_bounds__(T, (T <= 256 ? 3 : 1)) plicp2_kernel(PlicpArgs
     int iterations = 0, nvalid0 = 0, n_loops = 0, restarted = 0, valid_out = 0, status = ZHSM_JOB_OK;
     unsigned valid = 0;
     WalkDiag dg = {0, 0, 0};
+#ifdef PLICP_WALK_STATS
+    int st_arr[6] = {0, 0, 0, 0, 0, 0};
+    int *st_ = st_arr;
+#endif
 
     for (int loop = 0; loop < 7; loop++) {
         int iteration = 0, all_ok = 1, par = 0, newest = 0;
@@ -261,7 +286,7 @@ __global__ void __launch_bounds__(T, (T <= 256 ? 3 : 1)) plicp2_kernel(PlicpArgs
             it.cs = ctl->cs[par];
             it.sn = ctl->sn[par];
             if (t == 0) ctl->hash_acc[iteration & 1] = 0;
-            valid = find_correspondences<T>(l, wc, it, C, sens, iteration < a.chunk_iters, dg, pc);
+            valid = find_correspondences<T>(l, wc, it, C, sens, iteration < a.chunk_iters, dg, pc STATS_ARG);
             if (P.outliers_remove_doubles) {
                 for (int j = t; j < n; j += T) d2j[j] = BIG;  // the search used this area as its queue
                 __syncthreads();
@@ -495,7 +520,7 @@ __global__ void __launch_bounds__(T, (T <= 256 ? 3 : 1)) plicp2_kernel(PlicpArgs
         it.cs = ctl->cs[0];
         it.sn = ctl->sn[0];
         // "recompute correspondences in case of restarts" (icp.c): world coords at best x + tricks, no outlier pass
-        if (v_restarted) valid = find_correspondences<T>(l, wc, it, C, sens, a.chunk_iters > 0, dg, pc);
+        if (v_restarted) valid = find_correspondences<T>(l, wc, it, C, sens, a.chunk_iters > 0, dg, pc STATS_ARG);
     }
     if (t == 0) ctl->hash_acc[0] = 0;
 #pragma unroll 1
@@ -516,6 +541,15 @@ __global__ void __launch_bounds__(T, (T <= 256 ? 3 : 1)) plicp2_kernel(PlicpArgs
     const int walks_all = block_sum<T>(dg.walks, ctl->ired, 0);
 
     const int walks_first = block_sum<T>(dg.first, ctl->ired, 1);
+#ifdef PLICP_WALK_STATS
+    int sts[5];
+    for (int k = 0; k < 5; k++) sts[k] = block_sum<T>(st_arr[k], ctl->ired, k & 3), __syncthreads();
+    int stmax = st_arr[5];
+    for (int o = 16; o > 0; o >>= 1) stmax = max(stmax, __shfl_xor_sync(0xffffffffu, stmax, o));
+    if (lane == 0) atomicMax(&ctl->qn[0], stmax);
+    __syncthreads();
+    stmax = ctl->qn[0];
+#endif
     double cov[6] = {0, 0, 0, 0, 0, 0};
     if (v_ok && P.do_compute_covariance)
         covariance_exact<T>(l, n, C, a.cs, it.x0, it.x1, it.cs, it.sn, P.sigma, cov);
@@ -537,6 +571,10 @@ __global__ void __launch_bounds__(T, (T <= 256 ? 3 : 1)) plicp2_kernel(PlicpArgs
             r.corr_hash = ctl->hash_acc[0] & 0x7FFFFFFFu;
             for (int q = 0; q < 6; q++) r.cov[q] = cov[q];
         }
+#ifdef PLICP_WALK_STATS
+        for (int k = 0; k < 5; k++) r.cov[k] = (double)sts[k];
+        r.cov[5] = (double)stmax;
+#endif
 #ifdef PLICP_PHASE_TIMING
         pc.mark(10);
         pc.acc[5] += pc.acc[19];

@@ -72,11 +72,20 @@ __device__ __forceinline__ int lds_b32(unsigned a) {
     return v;
 }
 
+#ifdef PLICP_WALK_STATS
+static __device__ int g_walk_trips_dummy;
+#define g_walk_trips (*trips_out)
+#endif
+
 // One ray's walk.  Returns j1 (a fully valid correspondence) or -1 and j2 in *j2out.
 // State: up / down = next index to probe in each direction; stopped bit 0 / 1 = that direction has ended.
 // CSM initialises last_dist_up = 0 and last_dist_down = -1; the only use is "last_up < last_down", false for both
 // (0, -1) and (0, 0), so 0 serves for both.
-static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int last_best, int *j2out) {
+static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int last_best, int *j2out
+#ifdef PLICP_WALK_STATS
+                                              , int *trips_out
+#endif
+) {
     const float HALF_PI_F = 1.57079632679489662f;
     const int n = c.n, to = n - 1;
     const unsigned a_rr2 = c.rr2, a_refp = c.refp;
@@ -91,9 +100,15 @@ static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int 
     int up = we_start_at + 1, down = we_start_at;
     double last_up = 0, last_down = 0;
     int stopped = 0;
+#ifdef PLICP_WALK_STATS
+    int trips = 0;
+#endif
     const float fi_min = c.fi_min, dfi = c.dfi, phi = r.phi;
 #pragma unroll 1
     while (stopped != 3) {
+#ifdef PLICP_WALK_STATS
+        trips++;
+#endif
         const bool now_up = (stopped == 2) | ((stopped == 0) & (last_up < last_down));
         const int idx = now_up ? up : down;
         const int bit = now_up ? 1 : 2;
@@ -131,15 +146,23 @@ static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int 
                 if (stop) { stopped |= bit; continue; }
                 nidx = idx + (rr2 < rho2 ? (int)(short)hops : hops >> 16);
             }
+        } else {
+            nidx = idx + (hops >> 16);  // an invalid ref ray: its entries hold the skip over the whole invalid run
         }
         up = now_up ? nidx : up;
         down = now_up ? down : nidx;
     }
+#ifdef PLICP_WALK_STATS
+    g_walk_trips = trips;
+#endif
     if (j1 == -1 || best > c.maxd2) return -1;
     if (j1 == 0 || j1 == n - 1) return -1;
-    int j2up = -1, j2down = -1;
-    for (int j = j1 + 1; j < n; j++) if (lds_f64(a_rr2 + 8u * j) >= 0) { j2up = j; break; }
-    for (int j = j1 - 1; j >= 0; j--) if (lds_f64(a_rr2 + 8u * j) >= 0) { j2down = j; break; }
+    // nearest valid neighbours of j1 (0 < j1 < n-1): an invalid neighbour's table entry skips its whole run
+    int j2up = j1 + 1, j2down = j1 - 1;
+    if (lds_f64(a_rr2 + 8u * j2up) < 0) j2up += lds_b32(a_jt_up + 4u * j2up) >> 16;
+    if (lds_f64(a_rr2 + 8u * j2down) < 0) j2down += lds_b32(a_jt_dn + 4u * j2down) >> 16;
+    if (j2up >= n) j2up = -1;
+    if (j2down < 0) j2down = -1;
     if (j2up == -1 && j2down == -1) return -1;
     int j2;
     if (j2up == -1) j2 = j2down;

@@ -12,6 +12,7 @@ $BENCH > $out/${tag}_plain.log 2>&1 || { echo "plain bench failed"; tail -n 5 $o
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $out/${tag}_launches.csv $BENCH > $out/${tag}_ncu1.log 2>&1
 # one full capture of the dominant kernel
 ncu --set full --clock-control none --import-source on -k regex:plicp2_kernel -c 1 -f -o $out/${tag}_plicp $BENCH > $out/${tag}_ncu2.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:jump_tables_kernel -c 1 -f -o $out/${tag}_jump $BENCH > $out/${tag}_ncu2b.log 2>&1
 # the zhpsm and zhicp kernels: plain, then one full capture each
 python tools/gpu_probe_psm.py fr079 4 > $out/${tag}_psm_plain.log 2>&1 && \
   ncu --set full --clock-control none --import-source on -k regex:psm_kernel -c 2 -f -o $out/${tag}_psm python tools/gpu_probe_psm.py fr079 4 > $out/${tag}_ncu3.log 2>&1
