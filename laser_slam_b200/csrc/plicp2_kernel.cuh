@@ -52,11 +52,13 @@ __device__ __forceinline__ bool search_ray(const Lay &l, const WalkCtx &w, const
 #ifdef PLICP_WALK_STATS
     int trips = 0;
     const int j1 = tricks_one(w, ray, (int)PL_SH(const short, l.spec)[i], &j2, &trips);
+    const int fast = trips >> 16;
+    trips &= 0xffff;
     g_stats[0] += trips;
     g_stats[1] += trips > 32 ? trips : 0;
     g_stats[2] += trips > 32;
-    g_stats[3] += trips > 256 ? trips : 0;
-    g_stats[4] += trips > 256;
+    g_stats[3] += fast;
+    g_stats[4] += trips > 32 ? fast : 0;
     g_stats[5] = trips > g_stats[5] ? trips : g_stats[5];
 #else
     const int j1 = tricks_one(w, ray, (int)PL_SH(const short, l.spec)[i], &j2);

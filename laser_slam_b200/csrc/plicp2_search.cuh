@@ -77,6 +77,8 @@ static __device__ int g_walk_trips_dummy;
 #define g_walk_trips (*trips_out)
 #endif
 
+constexpr int WALK_BUDGET = 12;
+
 // One ray's walk.  Returns j1 (a fully valid correspondence) or -1 and j2 in *j2out.
 // State: up / down = next index to probe in each direction; stopped bit 0 / 1 = that direction has ended.
 // CSM initialises last_dist_up = 0 and last_dist_down = -1; the only use is "last_up < last_down", false for both
@@ -104,11 +106,15 @@ static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int 
     int trips = 0;
 #endif
     const float fi_min = c.fi_min, dfi = c.dfi, phi = r.phi;
+    // The general loop: the next probe goes where the last distance was smaller (or where the walk is still alive).
+    // A walk that is still running after WALK_BUDGET probes with one direction ended leaves for the loop below.
+    int budget = WALK_BUDGET;
 #pragma unroll 1
     while (stopped != 3) {
 #ifdef PLICP_WALK_STATS
         trips++;
 #endif
+        if (--budget < 0 && stopped != 0) break;
         const bool now_up = (stopped == 2) | ((stopped == 0) & (last_up < last_down));
         const int idx = now_up ? up : down;
         const int bit = now_up ? 1 : 2;
@@ -151,6 +157,45 @@ static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int 
         }
         up = now_up ? nidx : up;
         down = now_up ? down : nidx;
+    }
+    // One direction has ended and the other runs on alone: the same loop body with the direction fixed (no selects, no
+    // last distances).  The rare walks that cross most of the scan (about 1 in 600, 100+ probes) spend nearly all
+    // their probes here with one lane of the warp alive, and a whole search phase waits for them: instructions per
+    // probe are what counts.  Short walks never come here, so the warp does not serialise the two loops.
+    if (stopped != 3) {
+        const bool go_up = stopped == 2;
+        const int sdir = go_up ? 1 : -1;
+        const unsigned a_jt = go_up ? a_jt_up : a_jt_dn;
+        int idx = go_up ? up : down;
+#pragma unroll 1
+        while ((unsigned)idx <= (unsigned)to) {
+#ifdef PLICP_WALK_STATS
+            trips += 0x10001;
+#endif
+            const double rr2 = lds_f64(a_rr2 + 8u * idx);
+            const double2 q = lds_f64x2(a_refp + 16u * idx);
+            const int hops = lds_b32(a_jt + 4u * idx);
+            int hop = hops >> 16;  // an invalid ref ray: the skip over its whole run
+            if (rr2 >= 0) {
+                const double d = dist2(wx, wy, q.x, q.y);
+                const bool better = d < best;
+                j1 = better ? idx : j1;
+                best = better ? d : best;
+                hop = sdir;
+                if ((idx - start_cell) * sdir > 0) {
+                    const float dth = theta_f(fi_min, dfi, idx) - phi;
+                    const float sdth = go_up ? dth : -dth;
+                    if (sdth > HALF_PI_F) {
+                        if (rho2 > best) break;
+                    } else {
+                        const double cross = wx * q.y - wy * q.x;
+                        if (cross * cross > best * rr2) break;
+                    }
+                    hop = rr2 < rho2 ? (int)(short)hops : (hops >> 16);
+                }
+            }
+            idx += hop;
+        }
     }
 #ifdef PLICP_WALK_STATS
     g_walk_trips = trips;

@@ -20,5 +20,5 @@ r = res.cpu().numpy().view(zh.RESULT_DTYPE).reshape(-1)
 c = r["cov"]; w = r["reserved"][:, 0].astype(np.float64)
 print(f"walks/pair {w.mean():.0f}; probes/walk {c[:,0].sum()/w.sum():.2f}")
 print(f"walks > 32 probes: {100*c[:,2].sum()/w.sum():.2f} % of the walks, {100*c[:,1].sum()/c[:,0].sum():.1f} % of the probes")
-print(f"walks > 256 probes: {100*c[:,4].sum()/w.sum():.3f} % of the walks, {100*c[:,3].sum()/c[:,0].sum():.1f} % of the probes")
+print(f"probes in the one-direction loop: {100*c[:,3].sum()/c[:,0].sum():.1f} % of all, {100*c[:,4].sum()/max(c[:,1].sum(),1):.1f} % of the probes of walks > 32")
 print(f"longest walk per pair: mean {c[:,5].mean():.0f}, max {c[:,5].max():.0f}; pairs with a walk > 256: {100*(c[:,5]>256).mean():.1f} %")
