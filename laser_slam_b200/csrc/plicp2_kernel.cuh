@@ -184,7 +184,7 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
 }
 
 template <int T>
-__global__ void __launch_bounds__(T, (T <= 256 ? 3 : 1)) plicp2_kernel(PlicpArgs a) {
+__global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 3 : 1)) plicp2_kernel(PlicpArgs a) {
     constexpr int NW = T / 32;
     const int n = a.L.n;
     const int C = (n + T - 1) / T;
