@@ -31,6 +31,8 @@ struct Ctl {
     int next;           // run another icp_loop
     int fin;            // valid | restarted<<1
     int qn[2];          // re-search queue length (ping-pong over verify rounds)
+    int topbyte;        // radix select: guessed top byte of the trim keys (that of the last result)
+    int sel_below;      // radix select: keys whose top byte is below the guess
 };
 
 // byte offsets into the dynamic shared memory block

@@ -231,6 +231,7 @@ __global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 3 : 1)) plicp2_k
         PL_SH(short, l.spec)[i] = -1;
     }
     if (t == 0) {
+        ctl->topbyte = 0x3f;
         for (int k = 0; k < 3; k++) ctl->x[0][k] = a.first_guess ? a.first_guess[3 * (size_t)job + k] : 0.0;
         ctl->cs[0] = cos(ctl->x[0][2]);
         ctl->sn[0] = sin(ctl->x[0][2]);
@@ -324,19 +325,42 @@ __global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 3 : 1)) plicp2_k
                     if (dist2(wx, wy, q.x, q.y) > (3.0 * 3.0) * dj) valid &= ~(1u << k);
                 }
             }
-            for (int b = t; b < 256; b += T) PL_SH(int, l.hist)[b] = 0;
+            // all three histogram sets of the radix select; set 1 is filled by the key loop below (plicp2_select.cuh)
+            for (int b = t; b < 768; b += T) PL_SH(int, l.hist)[b] = 0;
+            if (t == 0) ctl->sel_below = 0;
+            const int top_guess = ctl->topbyte;
             pc.mark(4);
             const int kcnt = block_sum<T>(__popc(valid), ctl->ired, 2);  // all reads of d2j are done
-            // kill_outliers_trim: distance to the segment (j1,j2); keys go to shared memory
+            // kill_outliers_trim: distance to the segment (j1,j2); keys go to shared memory, and their
+            // second byte into the select's first histogram when the top byte is the guessed one
+            {
+                int *hist1 = PL_SH(int, l.hist) + 256;
+                short *cand1 = PL_SH(short, l.candi) + 512;
+                int nb = 0;
 #pragma unroll 1
-            for (int k = 0; k < C; k++) {
-                if (!(valid >> k & 1u)) continue;
-                const int i = k * T + t;
-                const double2 p = sensp[i];
-                const double wx = it.cs * p.x - it.sn * p.y + it.x0;
-                const double wy = it.sn * p.x + it.cs * p.y + it.x1;
-                const double2 q1 = refp[cj1[i]], q2 = refp[cj2[i]];
-                d2j[i] = (unsigned long long)__double_as_longlong(dist_to_segment(q1.x, q1.y, q2.x, q2.y, wx, wy));
+                for (int k = 0; k < C; k++) {
+                    if (!(valid >> k & 1u)) continue;
+                    const int i = k * T + t;
+                    const double2 p = sensp[i];
+                    const double wx = it.cs * p.x - it.sn * p.y + it.x0;
+                    const double wy = it.sn * p.x + it.cs * p.y + it.x1;
+                    const double2 q1 = refp[cj1[i]], q2 = refp[cj2[i]];
+                    const unsigned long long u =
+                        (unsigned long long)__double_as_longlong(dist_to_segment(q1.x, q1.y, q2.x, q2.y, wx, wy));
+                    d2j[i] = u;
+                    const int top = (int)(u >> 56);
+                    if (top == top_guess) {
+                        const int dg8 = (int)(u >> 48) & 255;
+                        atomicAdd(&hist1[dg8], 0x10001);
+                        cand1[dg8] = (short)i;
+                    } else if (top < top_guess) {
+                        nb++;
+                    }
+                }
+                if (__any_sync(0xffffffffu, nb)) {
+                    nb = __reduce_add_sync(0xffffffffu, nb);
+                    if (lane == 0) atomicAdd(&ctl->sel_below, nb);
+                }
             }
             pc.mark(16);
             int order = (int)floor(kcnt * P.outliers_maxPerc);
@@ -346,7 +370,8 @@ __global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 3 : 1)) plicp2_k
             order2 = order2 < kcnt - 1 ? order2 : kcnt - 1;
             order2 = order2 > 0 ? order2 : 0;
             double lim1, d_o2;
-            select2<T>(l, C, valid, order, order2, lim1, d_o2, pc);
+            select2<T>(l, C, valid, order, order2, top_guess, &ctl->sel_below, lim1, d_o2, pc);
+            if (t == 0) ctl->topbyte = (int)((unsigned long long)__double_as_longlong(lim1) >> 56);
             pc.mark(5);
             const double lim2 = P.outliers_adaptive_mult * d_o2;
             const double error_limit = lim1 < lim2 ? lim1 : lim2;

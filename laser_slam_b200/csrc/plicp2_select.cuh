@@ -24,9 +24,60 @@ __device__ __forceinline__ int block_sum(int v, int *ired, int slot) {
 // warp redundantly locates the buckets (no second barrier).  A bucket holding a single key ends that rank early
 // (the key's owner index is remembered next to the histogram); three rotating histogram sets make the zeroing of
 // the next set race-free.
+//
+// The first two passes cost no pass of their own.  Distances of one iteration share their top byte (sign + 7
+// exponent bits: 0x3f for 2^-15 <= d < 1, 0x3e below), so the loop that WRITES the keys (plicp2_kernel.cuh) already
+// histograms their second byte into set 1, for the keys whose top byte equals a guess (the top byte of the previous
+// iteration's result), and counts the keys below the guess.  When both ranks fall among the guessed keys -- all but
+// never otherwise -- the select continues at pass 2; else it starts over at pass 0.
+
+// bucket of rank rem[r] in a 256-bin histogram (both ranks packed 16:16), computed by every lane of a warp:
+// digit[r], the rank inside that bucket nrem[r], the bucket's population cnt[r].  total[r] = keys in the histogram.
+__device__ __forceinline__ void locate2(const int *hist, int lane, const int rem[2], int digit[2], int nrem[2],
+                                        int cnt[2], int total[2]) {
+    int loc[8];
+#pragma unroll
+    for (int q = 0; q < 8; q++) loc[q] = hist[lane * 8 + q];
+    int sum = 0;  // packed: the low halves cannot carry into the high ones (fewer than 65536 keys)
+#pragma unroll
+    for (int q = 0; q < 8; q++) sum += loc[q];
+    int incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    const int tot = __shfl_sync(0xffffffffu, incl, 31);
+#pragma unroll
+    for (int r = 0; r < 2; r++) {
+        const int sum_r = (sum >> (16 * r)) & 0xffff, incl_r = (incl >> (16 * r)) & 0xffff;
+        const int excl = incl_r - sum_r;
+        const bool mine = rem[r] >= excl && rem[r] < incl_r;
+        int bsel = 0, acc = excl, cb = 0;
+        bool found = false;
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+            const int c = (loc[q] >> (16 * r)) & 0xffff;
+            const bool hit = !found && rem[r] < acc + c;
+            bsel = hit ? q : bsel;
+            cb = hit ? c : cb;
+            found |= hit;
+            acc = found ? acc : acc + c;
+        }
+        const unsigned who = __ballot_sync(0xffffffffu, mine);
+        const int src = who ? __ffs(who) - 1 : 0;  // exactly one lane when the rank is inside the population
+        digit[r] = __shfl_sync(0xffffffffu, lane * 8 + bsel, src);
+        nrem[r] = __shfl_sync(0xffffffffu, rem[r] - acc, src);
+        cnt[r] = __shfl_sync(0xffffffffu, cb, src);
+        total[r] = (tot >> (16 * r)) & 0xffff;
+    }
+}
+
+// top_guess / nbelow: the guessed top byte and the number of keys whose top byte is below it (see above); the keys'
+// second-byte histogram is in set 1, the owner of a key per bucket in cand set 1 (first half).
 template <int T, class Clock>
-__device__ __forceinline__ void select2(const Lay &l, int C, unsigned valid, int rank0, int rank1, double &v0,
-                                        double &v1, Clock &pc) {
+__device__ __forceinline__ void select2(const Lay &l, int C, unsigned valid, int rank0, int rank1, int top_guess,
+                                        const int *nbelow_p, double &v0, double &v1, Clock &pc) {
     const int t = threadIdx.x, lane = t & 31;
     const unsigned long long *keyS = PL_SH(const unsigned long long, l.d2j);
     int *hist_all = PL_SH(int, l.hist);
@@ -35,9 +86,33 @@ __device__ __forceinline__ void select2(const Lay &l, int C, unsigned valid, int
     int rem[2] = {rank0, rank1};
     bool done[2] = {false, false};
     double val[2] = {0, 0};
-    // set 0 is zeroed by the caller before the barrier that precedes this call
+    int first_pass = 0;
+    __syncthreads();  // the keys, their histogram (set 1) and *nbelow_p are in place
+    pc.mark(18);
+    {
+        const int nbelow = *nbelow_p;
+        // the fused passes 0+1: set 1 holds the second byte of the keys with the guessed top byte
+        const int r2[2] = {rank0 - nbelow, rank1 - nbelow};
+        int digit[2], nrem[2], cnt[2], total[2];
+        locate2(hist_all + 256, lane, r2, digit, nrem, cnt, total);
+        if (r2[0] >= 0 && r2[0] < total[0] && r2[1] >= 0 && r2[1] < total[1]) {
+            first_pass = 2;
+#pragma unroll
+            for (int r = 0; r < 2; r++) {
+                prefix[r] = ((unsigned long long)top_guess << 8) | (unsigned long long)digit[r];
+                rem[r] = nrem[r];
+                if (cnt[r] == 1) {
+                    done[r] = true;
+                    val[r] = __longlong_as_double((long long)keyS[cand_all[512 + digit[r]]]);
+                }
+            }
+        } else {
+            __syncthreads();  // slow warps may still be reading set 1, which pass 0 is about to zero
+        }
+    }
+    pc.mark(19);
 #pragma unroll 1
-    for (int pass = 0; pass < 8; pass++) {
+    for (int pass = first_pass; pass < 8 && !(done[0] && done[1]); pass++) {
         const int shift = 56 - 8 * pass;
         int *hist = hist_all + 256 * (pass % 3);
         short *cand = cand_all + 512 * (pass % 3);
@@ -57,50 +132,20 @@ __device__ __forceinline__ void select2(const Lay &l, int C, unsigned valid, int
         }
         __syncthreads();
         pc.mark(18);
-        int loc[8];
-#pragma unroll
-        for (int q = 0; q < 8; q++) loc[q] = hist[lane * 8 + q];
+        int digit[2], nrem[2], cnt[2], total[2];
+        locate2(hist, lane, rem, digit, nrem, cnt, total);
 #pragma unroll
         for (int r = 0; r < 2; r++) {
             if (done[r]) continue;
-            int sum = 0;
-#pragma unroll
-            for (int q = 0; q < 8; q++) sum += (loc[q] >> (16 * r)) & 0xffff;
-            int incl = sum;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                int v = __shfl_up_sync(0xffffffffu, incl, o);
-                if (lane >= o) incl += v;
-            }
-            const int excl = incl - sum;
-            const bool mine = rem[r] >= excl && rem[r] < incl;
-            int bsel = 0, acc = excl, cb = 0;
-            if (mine) {
-                bool found = false;
-#pragma unroll
-                for (int q = 0; q < 8; q++) {
-                    const int c = (loc[q] >> (16 * r)) & 0xffff;
-                    if (!found) {
-                        if (rem[r] < acc + c) { bsel = q; cb = c; found = true; }
-                        else acc += c;
-                    }
-                }
-            }
-            const unsigned who = __ballot_sync(0xffffffffu, mine);
-            const int src = __ffs(who) - 1;  // exactly one lane when the rank is inside the population
-            const int digit = __shfl_sync(0xffffffffu, lane * 8 + bsel, src < 0 ? 0 : src);
-            const int nrem = __shfl_sync(0xffffffffu, rem[r] - acc, src < 0 ? 0 : src);
-            const int cnt = __shfl_sync(0xffffffffu, cb, src < 0 ? 0 : src);
-            prefix[r] = (prefix[r] << 8) | (unsigned long long)digit;
-            rem[r] = nrem;
-            if (cnt == 1 || pass == 7) {
+            prefix[r] = (prefix[r] << 8) | (unsigned long long)digit[r];
+            rem[r] = nrem[r];
+            if (cnt[r] == 1 || pass == 7) {
                 done[r] = true;
                 val[r] = pass == 7 ? __longlong_as_double((long long)prefix[r])
-                                   : __longlong_as_double((long long)keyS[cand[256 * r + digit]]);
+                                   : __longlong_as_double((long long)keyS[cand[256 * r + digit[r]]]);
             }
         }
         pc.mark(19);
-        if (done[0] && done[1]) break;
     }
     v0 = val[0];
     v1 = val[1];
