@@ -47,6 +47,26 @@ print(f"    valid starts {r['valid'].mean():.3f}; iterations/start {r['iteration
 w = r["reserved"].astype(np.float64)
 print(f"    walks per start: {w[..., 0].mean():.0f} executed for {w[..., 1].mean():.0f} sequential ({w[..., 0].sum() / w[..., 1].sum():.2f}x); "
       f"re-search warp rounds {w[..., 2].mean():.0f}; kernel {kms / (P * G) * 148 * 1e3:.0f} us of SM time per start")
+if os.environ.get("ZHSM_LIB_VARIANT") == "timing":  # per-phase cycle counters instead of the result (tools/gpu_probe_phases.py)
+    q = r.reshape(-1)
+    ph = np.concatenate([q["x"], q["cov"], q["error"][:, None], q["goodness"][:, None].astype(np.float64), q["quality"][:, None].astype(np.float64),
+                         q["nvalid"][:, None].astype(np.float64), q["reserved"][:, 3:4].astype(np.float64),
+                         q["corr_hash"][:, None].astype(np.float64), q["n_loops"][:, None].astype(np.float64),
+                         q["reserved"][:, 0:3].astype(np.float64)], axis=1)
+    names = ["load", "jump tables", "first-pass walk", "verify + re-search", "kill doubles", "select: bucket search", "kill + GPC sums", "corr hash",
+             "solve: pose_diff, cos/sin, barrier", "loop control", "final corr/hash/cov", "solve: cross-warp sums", "solve: quartic coefficients",
+             "solve: greatest root", "solve: 4x4 system", "solve: atan2", "trim: keys", "(unused)", "select: histogram passes + barrier"]
+    tot = ph.sum(1)
+    print(f"    cycles/job {tot.mean():.0f}")
+    for k, nm in enumerate(names):
+        print(f"      {nm:36s} {ph[:, k].mean():10.0f} cycles/job  {100 * ph[:, k].sum() / tot.sum():5.1f} %")
+    sys.exit(0)
+if os.environ.get("ZHSM_LIB_VARIANT") == "stats":  # walk-length counters instead of cov[] (tools/gpu_probe_walkstats.py)
+    c = r["cov"].reshape(-1, 6); wa = w[..., 0].reshape(-1)
+    print(f"    probes/walk {c[:,0].sum()/wa.sum():.2f}; walks > 32 probes: {100*c[:,2].sum()/wa.sum():.2f} % of the walks, {100*c[:,1].sum()/c[:,0].sum():.1f} % of the probes; "
+          f"one-direction loop {100*c[:,3].sum()/c[:,0].sum():.1f} % of the probes; longest walk per start: mean {c[:,5].mean():.0f}, max {c[:,5].max():.0f}; "
+          f"probes/start {c[:,0].mean():.0f}, in walks > 32: {c[:,1].mean():.0f}, walks > 32 per start {c[:,2].mean():.1f}")
+    sys.exit(0)
 # parity sample against the CPU restatement
 K = 512
 fm = scans[: 2 * (K // G)].cpu().numpy()
