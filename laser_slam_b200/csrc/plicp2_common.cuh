@@ -38,18 +38,19 @@ struct Ctl {
 // byte offsets into the dynamic shared memory block
 struct Lay {
     unsigned refp;   // double2[n] ref points ("world" frame = ref sensor frame); NaN when invalid
-    unsigned sensp;  // double2[n] sens points, sens sensor frame; x = NaN when invalid
+    unsigned sensr;  // float[n]  sens readings [cm] as they came, -1 when invalid: the point is rebuilt on use (sens_point)
     unsigned rr2;    // double[n]  squared ref reading [m^2], -1 when invalid
     unsigned d2j;    // u64[n]     min dist2 per ref index (kill_outliers_double); then the trim keys per sens ray
     unsigned red;    // double[nwarps][NSUM]
     unsigned ctl;    // Ctl
-    unsigned hist;   // int[3][256]   radix-select histograms (both ranks packed 16:16)
+    unsigned hist;   // int[3][256]   radix-select histograms (both ranks packed 16:16); on the jump tables when they fit
     unsigned candi;  // short[3][2][256] radix-select: a ray index per bucket
     unsigned cj1;    // short[n] current correspondences (-1 none): fixpoint exchange, hash stream, output
     unsigned cj2;    // short[n]
     unsigned spec;   // short[n] last_best each ray was (or will be) searched with
     unsigned jt;     // short[2][n][2] pairs (up_bigger, up_smaller)[n], (down_bigger, down_smaller)[n]
     unsigned total;
+    bool jt_shared;  // hist/candi lie on top of jt: the jump tables are copied in again before every search
 };
 
 __host__ __device__ inline unsigned align16(unsigned b) { return (b + 15u) & ~15u; }
@@ -59,17 +60,21 @@ __host__ __device__ inline Lay make_layout(int n, int nthreads) {
     Lay l;
     unsigned o = 0;
     l.refp = o;  o += 16u * un;
-    l.sensp = o; o += 16u * un;
+    l.sensr = o; o += align16(4u * un);
     l.rr2 = o;   o += 8u * un;
     l.d2j = o;   o += 8u * un;
     l.red = o;   o += 8u * nw * NSUM;
     l.ctl = o;   o += align16((unsigned)sizeof(Ctl));
-    l.hist = o;  o += 4u * 768;
-    l.candi = o; o += 2u * 1536;
+    l.jt_shared = 8u * un >= 4u * 768 + 2u * 1536;
+    if (!l.jt_shared) {
+        l.hist = o;  o += 4u * 768;
+        l.candi = o; o += 2u * 1536;
+    }
     l.cj1 = o;   o += align16(2u * un);
     l.cj2 = o;   o += align16(2u * un);
     l.spec = o;  o += align16(2u * un);
     l.jt = o;    o += align16(8u * un);
+    if (l.jt_shared) { l.hist = l.jt; l.candi = l.jt + 4u * 768; }
     l.total = align16(o);
     return l;
 }
@@ -104,6 +109,19 @@ __device__ __forceinline__ double dist_to_segment(double ax, double ay, double b
     if ((projx - ax) * (projx - bx) + (projy - ay) * (projy - by) < 0) return distance;
     double da = dist2(ax, ay, x, y), db = dist2(bx, by, x, y);
     return sqrt(da < db ? da : db);
+}
+
+// A sens point in the sens sensor frame, rebuilt from its float reading [cm] and the (cos, sin) table of the handle
+// (global memory, L1-resident) exactly as the load phase of the reference builds it: m = (double)f / 100.0, then
+// (cos * m, sin * m).  The quotient is formed without a division: q0 = f * 0.01, one FMA residual, one FMA correction
+// is the correctly rounded f / 100 (Markstein; checked exhaustively for every float in [2^-20, 2^20)).  Keeping 4
+// bytes per sens ray instead of a double2 is what lets one more CTA fit an SM.  Valid rays only.
+__device__ __forceinline__ double2 sens_point(const float *sensr, const double2 *cs, int i) {
+    const double r = (double)sensr[i];
+    const double q0 = r * 0.01;
+    const double m = fma(fma(-q0, 100.0, r), 0.01, q0);
+    const double2 c = __ldg(cs + i);
+    return make_double2(c.x * m, c.y * m);
 }
 
 // fromPMScan2LDP (:198-208) + ld_valid_fields' per-ray check + ld_invalid_if_outside.

@@ -85,7 +85,8 @@ template <int T>
 __device__ __forceinline__ void covariance_exact(const Lay &l, int n, int C, const double2 *cs_table, double x0,
                                                  double x1, double ct, double st, double sigma, double cov[6]) {
     const int t = threadIdx.x;
-    const double2 *refp = PL_SH(const double2, l.refp), *sensp = PL_SH(const double2, l.sensp);
+    const double2 *refp = PL_SH(const double2, l.refp);
+    const float *sensr = PL_SH(const float, l.sensr);
     const short *cj1 = PL_SH(const short, l.cj1), *cj2 = PL_SH(const short, l.cj2);
     double *g1x = PL_SH(double, l.rr2), *g1y = PL_SH(double, l.d2j), *g1t = PL_SH(double, l.jt);
     double *red = PL_SH(double, l.red);
@@ -102,7 +103,7 @@ __device__ __forceinline__ void covariance_exact(const Lay &l, int n, int C, con
         const int j1 = cj1[i];
         if (j1 < 0) continue;
         const int j2 = cj2[i];
-        const double2 p = sensp[i], q1 = refp[j1], q2 = refp[j2];
+        const double2 p = sens_point(sensr, cs_table, i), q1 = refp[j1], q2 = refp[j2];
         // rotations of p by theta + pi/2 and theta + pi: (-st, ct) and (-ct, -st)
         const double v1x = -st * p.x - ct * p.y, v1y = ct * p.x - st * p.y;
         const double v2x = ct * p.x - st * p.y + x0 - q1.x, v2y = st * p.x + ct * p.y + x1 - q1.y;

@@ -11,11 +11,14 @@ cudaError_t plicp_launch_t192(const PlicpArgs &a, cudaStream_t st);
 cudaError_t plicp_launch_t256(const PlicpArgs &a, cudaStream_t st);
 cudaError_t plicp_launch_t512(const PlicpArgs &a, cudaStream_t st);
 
-// CTA size per beam count: enough threads that a thread owns <= ~5 rays, and as many resident CTAs per SM as the
-// shared-memory footprint (~68 B per beam) allows.  ZHSM_PLICP_T overrides (tuning only; measured at 1080 beams on one
-// B200, 20k pairs: T=256 17.57 ms, 224 17.65, 288 17.98, 192 18.87 -- and at 768 beams 192 x 4 CTAs/SM 11.04 vs 256 x 3 11.60).
+// CTA size per beam count: as many resident CTAs per SM as the shared-memory footprint (~51 B per beam) and the
+// registers (80 per thread up to 256 threads) allow -- a job has serial stretches (the solve, the tail of a search
+// round) that only other jobs on the same SM can fill -- and then enough threads that a thread owns <= ~8 rays:
+//   n <= 640: 128 threads;  n <= 1152: 192 (4 CTAs/SM at 1080 beams);  n <= 2304: 256 (2 CTAs/SM at 2048);  else 512.
+// ZHSM_PLICP_T overrides (tuning only; measured on one B200: 1080 beams, 20k pairs: 192 threads 16.79 ms, 256 17.51;
+// 2048 beams, first guess 0, 4000 pairs: 256 threads 46.7 ms, 512 (1 CTA/SM) 72.0; C5 multi-start 44.4k vs 30.1k/s).
 void plicp_shape(int n, int *T, int *C, int *hash_chunk) {
-    int t = n <= 640 ? 128 : (n <= 1536 ? 256 : 512);
+    int t = n <= 640 ? 128 : n <= 1152 ? 192 : n <= 2304 ? 256 : 512;
     if (const char *e = getenv("ZHSM_PLICP_T")) {
         int v = atoi(e);
         if (v == 128 || v == 192 || v == 256 || v == 512) t = v;

@@ -33,6 +33,7 @@ struct WalkDiag {
 struct IterCtx {
     double x0, x1, cs, sn;
     double min_theta, C1;
+    const double2 *cs2;  // (cos, sin) of the beam angles (handle table, global memory)
 };
 
 #ifdef PLICP_WALK_STATS
@@ -47,7 +48,7 @@ struct IterCtx {
 
 // search sens ray i with its speculated last_best; returns true when it got a correspondence
 __device__ __forceinline__ bool search_ray(const Lay &l, const WalkCtx &w, const IterCtx &it, int i STATS_PARAM) {
-    const Ray ray = make_ray(PL_SH(const double2, l.sensp)[i], it.x0, it.x1, it.cs, it.sn, it.min_theta, it.C1);
+    const Ray ray = make_ray(sens_point(PL_SH(const float, l.sensr), it.cs2, i), it.x0, it.x1, it.cs, it.sn, it.min_theta, it.C1);
     int j2 = -1;
 #ifdef PLICP_WALK_STATS
     int trips = 0;
@@ -79,13 +80,21 @@ __device__ __forceinline__ bool search_ray(const Lay &l, const WalkCtx &w, const
 // sens: bit k = ray k*T+t exists and is valid; returns the mask of those rays holding a correspondence.
 template <int T>
 __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const WalkCtx &w, const IterCtx &it, int C,
-                                                         unsigned sens, bool chunked, WalkDiag &dg, PhaseClock &pc STATS_PARAM) {
+                                                         unsigned sens, bool chunked, const uint2 *jt_src, WalkDiag &dg,
+                                                         PhaseClock &pc STATS_PARAM) {
     constexpr int NW = T / 32;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int n = w.n;
     const unsigned lane_lt = (1u << lane) - 1u;
     Ctl *ctl = PL_SH(Ctl, l.ctl);
     if (t == 0) ctl->qn[0] = 0;
+    if (jt_src) {
+        // the radix select's histograms share the jump tables' shared memory (Lay::jt_shared): bring the tables back
+        // (8 bytes per ray from this job's scratch, L2-resident)
+        uint2 *dst = PL_SH(uint2, l.jt);
+        for (int q = t; q < n; q += T) dst[q] = __ldg(jt_src + q);
+        __syncthreads();
+    }
     if (!chunked) {
 #pragma unroll 1
         for (int k = 0; k < C; k++)
@@ -97,7 +106,7 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
     } else {
         // thread t walks the rays [t*C, (t+1)*C) in order and hands last_best from one to the next: only the first
         // ray of a chunk is speculated
-        const double2 *sensp = PL_SH(const double2, l.sensp);
+        const float *sensr = PL_SH(const float, l.sensr);
         short *specw = PL_SH(short, l.spec);
         const short *cj1r = PL_SH(const short, l.cj1);
         int lb = 0;
@@ -106,7 +115,7 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
         for (int q = 0; q < C; q++) {
             const int i = t * C + q;
             if (i >= n) break;
-            if (sensp[i].x != sensp[i].x) continue;  // invalid sens ray: no walk, last_best unchanged
+            if (sensr[i] < 0) continue;  // invalid sens ray: no walk, last_best unchanged
             if (have) specw[i] = (short)lb;
             dg.walks++;
             dg.first++;
@@ -194,7 +203,8 @@ __global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 3 : 1)) plicp2_k
     Ctl *ctl = PL_SH(Ctl, l.ctl);
     const LaserDev L = a.L;
     const zhsm_plicp_params &P = a.P;
-    double2 *refp = PL_SH(double2, l.refp), *sensp = PL_SH(double2, l.sensp);
+    double2 *refp = PL_SH(double2, l.refp);
+    float *sensr = PL_SH(float, l.sensr);
     double *rr2a = PL_SH(double, l.rr2);
     unsigned long long *d2j = PL_SH(unsigned long long, l.d2j);
     short *cj1 = PL_SH(short, l.cj1), *cj2 = PL_SH(short, l.cj2);
@@ -207,12 +217,13 @@ __global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 3 : 1)) plicp2_k
     const float *sens_row = a.scans + (size_t)a.sens_idx[job] * n;
     int bad_field = 0, nvf_ref = 0, nvf_sens = 0;
     unsigned sens = 0;
-    {
-        // jump tables of this job's ref scan, built by jump_tables_kernel (plicp2_jump.cu): 8 bytes per ray
-        const uint2 *src = reinterpret_cast<const uint2 *>(a.jt + (size_t)job * 4 * n);
+    // jump tables of this job's ref scan, built by jump_tables_kernel (plicp2_jump.cu): 8 bytes per ray
+    const uint2 *jt_job = reinterpret_cast<const uint2 *>(a.jt + (size_t)job * 4 * n);
+    if (!l.jt_shared) {
         uint2 *dst = PL_SH(uint2, l.jt);
-        for (int q = t; q < n; q += T) dst[q] = __ldg(src + q);
+        for (int q = t; q < n; q += T) dst[q] = __ldg(jt_job + q);
     }
+    const uint2 *jt_src = l.jt_shared ? jt_job : nullptr;  // find_correspondences copies them in before every search
 #pragma unroll 1
     for (int k = 0; k < C; k++) {
         const int i = k * T + t;
@@ -222,9 +233,10 @@ __global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 3 : 1)) plicp2_k
         nvf_ref += (rr != -1.0);
         rr2a[i] = rr >= 0 ? rr * rr : -1.0;
         refp[i] = rr >= 0 ? make_double2(cs.x * rr, cs.y * rr) : make_double2(nan(""), nan(""));
-        double rs = reading_of(__ldg(sens_row + i), L, P, &bad_field);
+        const float fs = __ldg(sens_row + i);
+        double rs = reading_of(fs, L, P, &bad_field);
         nvf_sens += (rs != -1.0);
-        sensp[i] = rs >= 0 ? make_double2(cs.x * rs, cs.y * rs) : make_double2(nan(""), nan(""));
+        sensr[i] = rs >= 0 ? fs : -1.f;
         if (rs >= 0) sens |= 1u << k;
         cj1[i] = -1;
         cj2[i] = -1;
@@ -258,6 +270,7 @@ __global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 3 : 1)) plicp2_k
     pc.mark(0);  // the block sums above were barriers: the tables are in place
 
     IterCtx it;
+    it.cs2 = a.cs;
     it.min_theta = (double)theta_f(L.fi_min, L.dfi, 0);
     it.C1 = (double)n / ((double)theta_f(L.fi_min, L.dfi, n - 1) - it.min_theta);
     WalkCtx wc;
@@ -289,7 +302,7 @@ __global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 3 : 1)) plicp2_k
             it.cs = ctl->cs[par];
             it.sn = ctl->sn[par];
             if (t == 0) ctl->hash_acc[iteration & 1] = 0;
-            valid = find_correspondences<T>(l, wc, it, C, sens, iteration < a.chunk_iters, dg, pc STATS_ARG);
+            valid = find_correspondences<T>(l, wc, it, C, sens, iteration < a.chunk_iters, jt_src, dg, pc STATS_ARG);
             if (P.outliers_remove_doubles) {
                 for (int j = t; j < n; j += T) d2j[j] = BIG;  // the search used this area as its queue
                 __syncthreads();
@@ -301,7 +314,7 @@ __global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 3 : 1)) plicp2_k
                 for (int k = 0; k < C; k++) {
                     if (!(valid >> k & 1u)) continue;
                     const int i = k * T + t;
-                    const double2 p = sensp[i];
+                    const double2 p = sens_point(sensr, a.cs, i);
                     const double wx = it.cs * p.x - it.sn * p.y + it.x0;
                     const double wy = it.sn * p.x + it.cs * p.y + it.x1;
                     const int j1 = cj1[i];
@@ -316,7 +329,7 @@ __global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 3 : 1)) plicp2_k
                 for (int k = 0; k < C; k++) {
                     if (!(valid >> k & 1u)) continue;
                     const int i = k * T + t;
-                    const double2 p = sensp[i];
+                    const double2 p = sens_point(sensr, a.cs, i);
                     const double wx = it.cs * p.x - it.sn * p.y + it.x0;
                     const double wy = it.sn * p.x + it.cs * p.y + it.x1;
                     const int j1 = cj1[i];
@@ -341,7 +354,7 @@ __global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 3 : 1)) plicp2_k
                 for (int k = 0; k < C; k++) {
                     if (!(valid >> k & 1u)) continue;
                     const int i = k * T + t;
-                    const double2 p = sensp[i];
+                    const double2 p = sens_point(sensr, a.cs, i);
                     const double wx = it.cs * p.x - it.sn * p.y + it.x0;
                     const double wy = it.sn * p.x + it.cs * p.y + it.x1;
                     const double2 q1 = refp[cj1[i]], q2 = refp[cj2[i]];
@@ -393,7 +406,7 @@ __global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 3 : 1)) plicp2_k
                         keep = true;
                         nkept++;
                         S[14] += key;
-                        const double2 p = sensp[i];
+                        const double2 p = sens_point(sensr, a.cs, i);
                         const double2 q1 = refp[cj1[i]], q2 = refp[cj2[i]];
                         const double px = p.x, py = p.y, qx = q1.x, qy = q1.y;
                         const double diff0 = q1.x - q2.x, diff1 = q1.y - q2.y;
@@ -547,7 +560,7 @@ __global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 3 : 1)) plicp2_k
         it.cs = ctl->cs[0];
         it.sn = ctl->sn[0];
         // "recompute correspondences in case of restarts" (icp.c): world coords at best x + tricks, no outlier pass
-        if (v_restarted) valid = find_correspondences<T>(l, wc, it, C, sens, a.chunk_iters > 0, dg, pc STATS_ARG);
+        if (v_restarted) valid = find_correspondences<T>(l, wc, it, C, sens, a.chunk_iters > 0, jt_src, dg, pc STATS_ARG);
     }
     if (t == 0) ctl->hash_acc[0] = 0;
 #pragma unroll 1
