@@ -29,7 +29,7 @@ FOV_DEG = 270.0
 MAX_RANGE_CM = 3000
 SEED = 20261104
 # dram__bytes_read.sum + dram__bytes_write.sum of plicp2_kernel per pair (profiles/r01c_*: 175.5 MB + 30.1 MB / 20000 pairs)
-NCU_DRAM_BYTES_PER_PAIR = (175.535360e6 + 30.145280e6) / 20000
+NCU_DRAM_BYTES_PER_PAIR = (348.270080e6 + 39.143680e6) / 20000  # profiles/r01j_plicp2_T192_raw_metrics.txt
 
 
 def make_laser(zh):
@@ -228,6 +228,8 @@ def run_ours(args):
     dev = torch.device(f"cuda:{local}")
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        # NCCL writes its version banner (and anything NCCL_DEBUG asks for) to stdout: keep stdout for the JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
     eng = zh.Engine(local)
     lz = make_laser(zh)

@@ -92,7 +92,7 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
         // the radix select's histograms share the jump tables' shared memory (Lay::jt_shared): bring the tables back
         // (8 bytes per ray from this job's scratch, L2-resident)
         uint2 *dst = PL_SH(uint2, l.jt);
-        for (int q = t; q < n; q += T) dst[q] = __ldg(jt_src + q);
+        for (int q = t; q < n; q += T) dst[q] = __ldcs(jt_src + q);  // streaming: leave the L1 to the cs table
         __syncthreads();
     }
     if (!chunked) {
@@ -221,7 +221,7 @@ __global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 3 : 1)) plicp2_k
     const uint2 *jt_job = reinterpret_cast<const uint2 *>(a.jt + (size_t)job * 4 * n);
     if (!l.jt_shared) {
         uint2 *dst = PL_SH(uint2, l.jt);
-        for (int q = t; q < n; q += T) dst[q] = __ldg(jt_job + q);
+        for (int q = t; q < n; q += T) dst[q] = __ldcs(jt_job + q);
     }
     const uint2 *jt_src = l.jt_shared ? jt_job : nullptr;  // find_correspondences copies them in before every search
 #pragma unroll 1
@@ -229,11 +229,11 @@ __global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 3 : 1)) plicp2_k
         const int i = k * T + t;
         if (i >= n) break;
         const double2 cs = a.cs[i];
-        double rr = reading_of(__ldg(ref_row + i), L, P, &bad_field);
+        double rr = reading_of(__ldcs(ref_row + i), L, P, &bad_field);
         nvf_ref += (rr != -1.0);
         rr2a[i] = rr >= 0 ? rr * rr : -1.0;
         refp[i] = rr >= 0 ? make_double2(cs.x * rr, cs.y * rr) : make_double2(nan(""), nan(""));
-        const float fs = __ldg(sens_row + i);
+        const float fs = __ldcs(sens_row + i);
         double rs = reading_of(fs, L, P, &bad_field);
         nvf_sens += (rs != -1.0);
         sensr[i] = rs >= 0 ? fs : -1.f;
