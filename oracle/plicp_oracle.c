@@ -998,3 +998,21 @@ void orc_median_filter_batch(float *scans, int S, int n, int nthreads) {
     for (int t = 0; t < nthreads; t++) pthread_create(&th[t], NULL, mf_worker, &jobs[t]);
     for (int t = 0; t < nthreads; t++) pthread_join(th[t], NULL);
 }
+
+/* Checker for the CUDA kernel's division-free reading conversion (laser_slam_b200/csrc/plicp2_common.cuh,
+ * sens_point): fromPMScan2LDP computes (double)f / 100.0 (src/zhcsm/ZHCanonical_Matcher.cpp:198-208); the kernel
+ * forms q0 = f * 0.01, r = fma(-q0, 100, f), q = fma(r, 0.01, q0).  Counts the floats with bit patterns in
+ * [lo_bits, hi_bits) for which the two differ (expected: none). */
+long long orc_count_div100_mismatches(unsigned lo_bits, unsigned hi_bits) {
+    long long bad = 0;
+    for (unsigned u = lo_bits; u < hi_bits; u++) {
+        float f;
+        memcpy(&f, &u, 4);
+        const double r = (double)f;
+        const double ref = r / 100.0;
+        const double q0 = r * 0.01;
+        const double q = fma(fma(-q0, 100.0, r), 0.01, q0);
+        bad += !(q == ref);
+    }
+    return bad;
+}

@@ -66,6 +66,8 @@ def lib():
                                                 C.c_float, C.c_int, C.c_int, C.POINTER(SmParams), C.c_void_p,
                                                 C.c_void_p, C.c_int]
         _lib.orc_poly_greatest_real_root.argtypes = [C.c_void_p, C.c_void_p]
+        _lib.orc_count_div100_mismatches.argtypes = [C.c_uint, C.c_uint]
+        _lib.orc_count_div100_mismatches.restype = C.c_longlong
         _lib.orc_poly_greatest_real_root.restype = C.c_int
     return _lib
 
@@ -120,6 +122,12 @@ def zhcsm_fmatch(ref_r_cm, sens_r_cm, fi_min, dfi, min_range_cm, max_range_cm, p
     if want_corr:
         out["j1"], out["j2"] = j1, j2
     return out
+
+
+def count_div100_mismatches(lo, hi):
+    """floats in [lo, hi) whose exact-FMA quotient f/100 (the CUDA kernel's) differs from the division"""
+    lo_b, hi_b = (int(np.float32(v).view(np.uint32)) for v in (lo, hi))
+    return int(lib().orc_count_div100_mismatches(lo_b, hi_b))
 
 
 def zhcsm_fmatch_batch(scans_cm, ref_idx, sens_idx, fi_min, dfi, min_range_cm, max_range_cm, params=None,

@@ -341,3 +341,10 @@ def test_graph_oracle_consensus_properties():
         d = np.hypot(*(poses[lo:hi, :2] - fp[s, :2]).T)
         assert fi[s] - lo == np.flatnonzero(k)[np.argmin(d[k])]
     assert 0.02 < 1 - keep.mean() < 0.2                               # some mismatches are dropped, most entries stay
+
+
+def test_division_free_reading_conversion_is_exact():
+    """The CUDA kernel rebuilds a sens point from its float reading with q0 = f * 0.01 and two FMAs instead of
+    fromPMScan2LDP's (double)f / 100.0 (src/zhcsm/ZHCanonical_Matcher.cpp:198-208).  Exhaustive over every float a
+    laser reading can be: 1 mm .. 2^17 cm."""
+    assert po.count_div100_mismatches(0.1, 131072.0) == 0
