@@ -228,9 +228,19 @@ def run_ours(args):
     dev = torch.device(f"cuda:{local}")
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        # NCCL writes its version banner (and anything NCCL_DEBUG asks for) to stdout: keep stdout for the JSON line
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
-        dist.init_process_group("nccl", device_id=dev)
+        # NCCL writes its version banner (and anything NCCL_DEBUG asks for) to stdout while the communicator comes
+        # up: stdout is for the one JSON line, so file descriptor 1 points at stderr until the first collective is done
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            dist.barrier(device_ids=[local])
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved_stdout, 1)
+            os.close(saved_stdout)
     eng = zh.Engine(local)
     lz = make_laser(zh)
     eng.set_laser(lz)

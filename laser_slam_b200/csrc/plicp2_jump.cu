@@ -12,7 +12,7 @@
 // again: at most 7+7+nb64+8+8 probes (47 at 1080 rays), 1-3 for the common short jumps.
 //
 // Why a separate kernel: the searches are chains of dependent shared-memory loads with divergent trip counts.
-// Inside the PL-ICP kernel (3 CTAs = 24 warps per SM, limited by its 75 KB of shared memory) that phase took 10 % of
+// Inside the PL-ICP kernel (24 warps per SM, limited by its shared memory) that phase took 10 % of
 // the job; here a CTA needs 5 KB, 64 warps per SM hide the latency, and the tables cost 8 bytes per
 // ray of HBM traffic each way (17 KB per job: nothing against 7.7 TB/s).
 //
