@@ -393,7 +393,7 @@ def run_ours(args):
                              "traffic": NCU_DRAM_BYTES_PER_PAIR * P,
                              "traffic_source": "ncu --set full dram__bytes_read+write of a 20k-pair launch "
                                                "(profiles/), scaled by pairs per launch",
-                             "kernel": "plicp2_kernel<%d>" % (128 if N_BEAMS <= 640 else 192 if N_BEAMS <= 1152 else 256 if N_BEAMS <= 2304 else 512), "kernel_ms": kern_ms,
+                             "kernel": "plicp2_kernel<%d>" % (128 if N_BEAMS <= 640 else 192 if N_BEAMS <= 1472 else 256 if N_BEAMS <= 2304 else 512), "kernel_ms": kern_ms,
                              "peak_source": "DFMA micro-benchmark measured in this run (zhsm_fp_peak_tflops)",
                              "fp32_peak": peak32, "frac_of_fp32_peak": achieved / peak32 if peak32 > 0 else None,
                              "algorithmic_flops_per_launch": flops, **fl_detail,

@@ -12,13 +12,16 @@ cudaError_t plicp_launch_t256(const PlicpArgs &a, cudaStream_t st);
 cudaError_t plicp_launch_t512(const PlicpArgs &a, cudaStream_t st);
 
 // CTA size per beam count: as many resident CTAs per SM as the shared-memory footprint (~51 B per beam) and the
-// registers (80 per thread up to 256 threads) allow -- a job has serial stretches (the solve, the tail of a search
-// round) that only other jobs on the same SM can fill -- and then enough threads that a thread owns <= ~8 rays:
-//   n <= 640: 128 threads;  n <= 1152: 192 (4 CTAs/SM at 1080 beams);  n <= 2304: 256 (2 CTAs/SM at 2048);  else 512.
-// ZHSM_PLICP_T overrides (tuning only; measured on one B200: 1080 beams, 20k pairs: 192 threads 16.79 ms, 256 17.51;
-// 2048 beams, first guess 0, 4000 pairs: 256 threads 46.7 ms, 512 (1 CTA/SM) 72.0; C5 multi-start 44.4k vs 30.1k/s).
+// registers allow -- a job has serial stretches (the solve, the tail of a search round) that only other jobs on the
+// same SM can fill -- and then enough threads that a thread owns <= ~8 rays:
+//   n <= 640: 128 threads;  n <= 1472: 192 threads, 80 registers (4 CTAs/SM at 1080 beams, 3 up to 1472);
+//   n <= 2304: 256 threads, 128 registers, 2 CTAs/SM (2048 beams), the COOP instance whose long walks are finished
+//   warp-wide (plicp2_search.cuh);  else 512 threads (COOP as well).
+// ZHSM_PLICP_T overrides (tuning only).  Measured on one B200: 1080 beams, 20k pairs: 192 threads 16.8 ms, 256 (2
+// CTAs/SM) 23.9; 1440 beams, 10k pairs: 192: 21.4 ms, 256: 22.1; 1536 beams: 192: 24.3, 256: 22.7; 2048 beams, first
+// guess 0, 4000 pairs: 256: 29.8 ms, 512 (1 CTA/SM): 36.6.
 void plicp_shape(int n, int *T, int *C, int *hash_chunk) {
-    int t = n <= 640 ? 128 : n <= 1152 ? 192 : n <= 2304 ? 256 : 512;
+    int t = n <= 640 ? 128 : n <= 1472 ? 192 : n <= 2304 ? 256 : 512;
     if (const char *e = getenv("ZHSM_PLICP_T")) {
         int v = atoi(e);
         if (v == 128 || v == 192 || v == 256 || v == 512) t = v;

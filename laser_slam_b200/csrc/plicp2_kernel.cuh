@@ -47,12 +47,13 @@ struct IterCtx {
 #endif
 
 // search sens ray i with its speculated last_best; returns true when it got a correspondence
+template <bool COOP>
 __device__ __forceinline__ bool search_ray(const Lay &l, const WalkCtx &w, const IterCtx &it, int i STATS_PARAM) {
     const Ray ray = make_ray(sens_point(PL_SH(const float, l.sensr), it.cs2, i), it.x0, it.x1, it.cs, it.sn, it.min_theta, it.C1);
     int j2 = -1;
 #ifdef PLICP_WALK_STATS
     int trips = 0;
-    const int j1 = tricks_one(w, ray, (int)PL_SH(const short, l.spec)[i], &j2, &trips);
+    const int j1 = tricks_one<false>(w, ray, (int)PL_SH(const short, l.spec)[i], &j2, nullptr, &trips);
     const int fast = trips >> 16;
     trips &= 0xffff;
     g_stats[0] += trips;
@@ -62,11 +63,50 @@ __device__ __forceinline__ bool search_ray(const Lay &l, const WalkCtx &w, const
     g_stats[4] += trips > 32 ? fast : 0;
     g_stats[5] = trips > g_stats[5] ? trips : g_stats[5];
 #else
-    const int j1 = tricks_one(w, ray, (int)PL_SH(const short, l.spec)[i], &j2);
+    const int j1 = tricks_one<false>(w, ray, (int)PL_SH(const short, l.spec)[i], &j2, nullptr);
 #endif
     PL_SH(short, l.cj1)[i] = (short)j1;
     PL_SH(short, l.cj2)[i] = (short)(j1 >= 0 ? j2 : -1);
     return j1 >= 0;
+}
+
+// COOP instances (long scans): search_ray_coop is called by ALL lanes of a warp (active = this lane has a ray).  Each
+// lane walks its own ray; the few walks that would keep a single lane busy for hundreds of probes come back
+// WALK_PENDING and are finished by the whole warp, one after the other (walk_warp_one / walk_warp_both).
+static __device__ __noinline__ void finish_pending(const Lay l, const WalkCtx w, const IterCtx it, int i, bool mine,
+                                                   WalkState *st, int *j1, int *j2) {
+    const unsigned FULL = 0xffffffffu;
+    Ray ray = {0.0, 0.0, 0.0, 0.0f, 0};
+    if (mine) ray = make_ray(sens_point(PL_SH(const float, l.sensr), it.cs2, i), it.x0, it.x1, it.cs, it.sn, it.min_theta, it.C1);
+    unsigned pend = __ballot_sync(FULL, mine);
+    while (pend) {
+        const int L = __ffs(pend) - 1;
+        pend &= pend - 1;
+        if (__shfl_sync(FULL, st->dir, L) == 2) walk_warp_both(w, L, ray, st);
+        else walk_warp_one(w, L, ray, st);
+    }
+    if (mine) *j1 = walk_finish(w, ray.wx, ray.wy, st->j1, st->best, j2);
+}
+
+__device__ __forceinline__ void search_ray_coop(const Lay &l, const WalkCtx &w, const IterCtx &it, int i, bool active STATS_PARAM) {
+    int j1 = -1, j2 = -1;
+    WalkState st;
+    st.dir = 0;
+    if (active) {
+        const Ray ray = make_ray(sens_point(PL_SH(const float, l.sensr), it.cs2, i), it.x0, it.x1, it.cs, it.sn, it.min_theta, it.C1);
+#ifdef PLICP_WALK_STATS
+        int trips = 0;
+        j1 = tricks_one<true>(w, ray, (int)PL_SH(const short, l.spec)[i], &j2, &st, &trips);
+        g_stats[0] += trips & 0xffff;
+#else
+        j1 = tricks_one<true>(w, ray, (int)PL_SH(const short, l.spec)[i], &j2, &st);
+#endif
+    }
+    if (__any_sync(0xffffffffu, j1 == WALK_PENDING)) finish_pending(l, w, it, i, j1 == WALK_PENDING, &st, &j1, &j2);
+    if (active) {
+        PL_SH(short, l.cj1)[i] = (short)j1;
+        PL_SH(short, l.cj2)[i] = (short)(j1 >= 0 ? j2 : -1);
+    }
 }
 
 // find_correspondences_tricks for the whole scan: speculate / verify / re-search until the sequential result.
@@ -83,6 +123,7 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
                                                          unsigned sens, bool chunked, const uint2 *jt_src, WalkDiag &dg,
                                                          PhaseClock &pc STATS_PARAM) {
     constexpr int NW = T / 32;
+    constexpr bool COOP = T >= 256;  // long scans: long walks are finished by the warp (plicp2_search.cuh)
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int n = w.n;
     const unsigned lane_lt = (1u << lane) - 1u;
@@ -97,12 +138,18 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
     }
     if (!chunked) {
 #pragma unroll 1
-        for (int k = 0; k < C; k++)
-            if (sens >> k & 1u) {
+        for (int k = 0; k < C; k++) {
+            if constexpr (COOP) {
+                const bool act = sens >> k & 1u;
+                dg.walks += act;
+                dg.first += act;
+                search_ray_coop(l, w, it, k * T + t, act STATS_ARG);
+            } else if (sens >> k & 1u) {
                 dg.walks++;
                 dg.first++;
-                search_ray(l, w, it, k * T + t STATS_ARG);
+                search_ray<false>(l, w, it, k * T + t STATS_ARG);
             }
+        }
     } else {
         // thread t walks the rays [t*C, (t+1)*C) in order and hands last_best from one to the next: only the first
         // ray of a chunk is speculated
@@ -111,18 +158,35 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
         const short *cj1r = PL_SH(const short, l.cj1);
         int lb = 0;
         bool have = false;
+        if constexpr (COOP) {
 #pragma unroll 1
-        for (int q = 0; q < C; q++) {
-            const int i = t * C + q;
-            if (i >= n) break;
-            if (sensr[i] < 0) continue;  // invalid sens ray: no walk, last_best unchanged
-            if (have) specw[i] = (short)lb;
-            dg.walks++;
-            dg.first++;
-            search_ray(l, w, it, i STATS_ARG);
-            const int c1 = cj1r[i];
-            lb = c1 >= 0 ? c1 : (int)specw[i];
-            have = true;
+            for (int q = 0; q < C; q++) {
+                const int i = t * C + q;
+                const bool act = i < n && !(sensr[i < n ? i : 0] < 0);  // an invalid sens ray: no walk, last_best unchanged
+                if (act && have) specw[i] = (short)lb;
+                dg.walks += act;
+                dg.first += act;
+                search_ray_coop(l, w, it, i, act STATS_ARG);
+                if (act) {
+                    const int c1 = cj1r[i];
+                    lb = c1 >= 0 ? c1 : (int)specw[i];
+                    have = true;
+                }
+            }
+        } else {
+#pragma unroll 1
+            for (int q = 0; q < C; q++) {
+                const int i = t * C + q;
+                if (i >= n) break;
+                if (sensr[i] < 0) continue;  // invalid sens ray: no walk, last_best unchanged
+                if (have) specw[i] = (short)lb;
+                dg.walks++;
+                dg.first++;
+                search_ray<false>(l, w, it, i STATS_ARG);
+                const int c1 = cj1r[i];
+                lb = c1 >= 0 ? c1 : (int)specw[i];
+                have = true;
+            }
         }
     }
     __syncthreads();
@@ -174,13 +238,25 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
         if (total == 0) break;
         dg.rounds++;
         int changed = 0;
+        if constexpr (COOP) {
 #pragma unroll 1
-        for (int e = t; e < total; e += T) {
-            const int i = (int)queue[e];
-            const int before = cj1[i];
-            dg.walks++;
-            search_ray(l, w, it, i STATS_ARG);
-            changed |= (int)cj1[i] != before;
+            for (int e = t; e - lane < total; e += T) {  // whole warps: the COOP search is a warp-wide call
+                const bool act = e < total;
+                const int i = act ? (int)queue[e] : 0;
+                const int before = cj1[i];
+                dg.walks += act;
+                search_ray_coop(l, w, it, i, act STATS_ARG);
+                changed |= act && (int)cj1[i] != before;
+            }
+        } else {
+#pragma unroll 1
+            for (int e = t; e < total; e += T) {
+                const int i = (int)queue[e];
+                const int before = cj1[i];
+                dg.walks++;
+                search_ray<false>(l, w, it, i STATS_ARG);
+                changed |= (int)cj1[i] != before;
+            }
         }
         if (!__syncthreads_or(changed)) break;  // last_best of every ray is what it was walked with
     }
@@ -193,7 +269,7 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
 }
 
 template <int T>
-__global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 3 : 1)) plicp2_kernel(PlicpArgs a) {
+__global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 2 : 1)) plicp2_kernel(PlicpArgs a) {
     constexpr int NW = T / 32;
     const int n = a.L.n;
     const int C = (n + T - 1) / T;

@@ -77,13 +77,52 @@ static __device__ int g_walk_trips_dummy;
 #define g_walk_trips (*trips_out)
 #endif
 
-constexpr int WALK_BUDGET = 12;
+// The end of every walk: the validity rules and j2.  Returns j1 (a fully valid correspondence) or -1, j2 in *j2out.
+__device__ __forceinline__ int walk_finish(const WalkCtx &c, double wx, double wy, int j1, double best, int *j2out) {
+    const int n = c.n;
+    const unsigned a_rr2 = c.rr2, a_refp = c.refp;
+    const unsigned a_jt_up = c.jt, a_jt_dn = c.jt + 4u * (unsigned)n;
+    if (j1 == -1 || best > c.maxd2) return -1;
+    if (j1 == 0 || j1 == n - 1) return -1;
+    // nearest valid neighbours of j1 (0 < j1 < n-1): an invalid neighbour's table entry skips its whole run
+    int j2up = j1 + 1, j2down = j1 - 1;
+    if (lds_f64(a_rr2 + 8u * j2up) < 0) j2up += lds_b32(a_jt_up + 4u * j2up) >> 16;
+    if (lds_f64(a_rr2 + 8u * j2down) < 0) j2down += lds_b32(a_jt_dn + 4u * j2down) >> 16;
+    if (j2up >= n) j2up = -1;
+    if (j2down < 0) j2down = -1;
+    if (j2up == -1 && j2down == -1) return -1;
+    int j2;
+    if (j2up == -1) j2 = j2down;
+    else if (j2down == -1) j2 = j2up;
+    else {
+        const double2 qu = lds_f64x2(a_refp + 16u * j2up), qd = lds_f64x2(a_refp + 16u * j2down);
+        j2 = dist2(wx, wy, qu.x, qu.y) < dist2(wx, wy, qd.x, qd.y) ? j2up : j2down;
+    }
+    *j2out = j2;
+    return j1;
+}
+
+constexpr int WALK_BUDGET = 12;    // probes of the general loop before a walk with one side ended leaves it
+constexpr int BOTH_AFTER = 28;     // COOP: further probes with both sides alive before the warp takes the walk over
+constexpr int SOLO_BUDGET = 24;    // COOP: probes of the one-direction loop before the warp takes the walk over
+constexpr int WALK_PENDING = -2;   // COOP: tricks_one returns this when the walk goes on with the whole warp
+
+// COOP (the instances for long scans, T >= 256): a walk that is still running after the budgets above is not
+// finished by its own lane -- hundreds of dependent probes while the rest of the CTA waits at the next barrier --
+// but handed to its warp (walk_warp_one / walk_warp_both below) in this state.
+struct WalkState {
+    double best, last_up, last_down;
+    int j1;
+    int up, down;  // next index to probe in each direction (dir = +-1: `up` holds the one index)
+    int dir;       // +1 / -1: one direction left; 2: both directions alive
+};
 
 // One ray's walk.  Returns j1 (a fully valid correspondence) or -1 and j2 in *j2out.
 // State: up / down = next index to probe in each direction; stopped bit 0 / 1 = that direction has ended.
 // CSM initialises last_dist_up = 0 and last_dist_down = -1; the only use is "last_up < last_down", false for both
 // (0, -1) and (0, 0), so 0 serves for both.
-static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int last_best, int *j2out
+template <bool COOP>
+static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int last_best, int *j2out, WalkState *out
 #ifdef PLICP_WALK_STATS
                                               , int *trips_out
 #endif
@@ -114,7 +153,17 @@ static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int 
 #ifdef PLICP_WALK_STATS
         trips++;
 #endif
-        if (--budget < 0 && stopped != 0) break;
+        if (--budget < 0) {
+            if (stopped != 0) break;
+            if (COOP && budget < -BOTH_AFTER) {
+                out->best = best; out->last_up = last_up; out->last_down = last_down;
+                out->j1 = j1; out->up = up; out->down = down; out->dir = 2;
+#ifdef PLICP_WALK_STATS
+                g_walk_trips = trips;
+#endif
+                return WALK_PENDING;
+            }
+        }
         const bool now_up = (stopped == 2) | ((stopped == 0) & (last_up < last_down));
         const int idx = now_up ? up : down;
         const int bit = now_up ? 1 : 2;
@@ -167,8 +216,17 @@ static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int 
         const int sdir = go_up ? 1 : -1;
         const unsigned a_jt = go_up ? a_jt_up : a_jt_dn;
         int idx = go_up ? up : down;
+        int solo = SOLO_BUDGET;
 #pragma unroll 1
         while ((unsigned)idx <= (unsigned)to) {
+            if (COOP && --solo < 0) {
+                out->best = best; out->last_up = 0; out->last_down = 0;
+                out->j1 = j1; out->up = idx; out->down = 0; out->dir = sdir;
+#ifdef PLICP_WALK_STATS
+                g_walk_trips = trips;
+#endif
+                return WALK_PENDING;
+            }
 #ifdef PLICP_WALK_STATS
             trips += 0x10001;
 #endif
@@ -200,24 +258,206 @@ static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int 
 #ifdef PLICP_WALK_STATS
     g_walk_trips = trips;
 #endif
-    if (j1 == -1 || best > c.maxd2) return -1;
-    if (j1 == 0 || j1 == n - 1) return -1;
-    // nearest valid neighbours of j1 (0 < j1 < n-1): an invalid neighbour's table entry skips its whole run
-    int j2up = j1 + 1, j2down = j1 - 1;
-    if (lds_f64(a_rr2 + 8u * j2up) < 0) j2up += lds_b32(a_jt_up + 4u * j2up) >> 16;
-    if (lds_f64(a_rr2 + 8u * j2down) < 0) j2down += lds_b32(a_jt_dn + 4u * j2down) >> 16;
-    if (j2up >= n) j2up = -1;
-    if (j2down < 0) j2down = -1;
-    if (j2up == -1 && j2down == -1) return -1;
-    int j2;
-    if (j2up == -1) j2 = j2down;
-    else if (j2down == -1) j2 = j2up;
-    else {
-        const double2 qu = lds_f64x2(a_refp + 16u * j2up), qd = lds_f64x2(a_refp + 16u * j2down);
-        j2 = dist2(wx, wy, qu.x, qu.y) < dist2(wx, wy, qd.x, qd.y) ? j2up : j2down;
+    return walk_finish(c, wx, wy, j1, best, j2out);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// COOP: the rest of a long walk, run by all 32 lanes of the warp for ONE ray (lane L's; its data is broadcast).
+//
+// The indices a direction probes do not depend on the distances found: from idx the walk goes to idx + hop(idx), hop
+// being a unit step before the start cell, a jump-table entry chosen by `rr2 < rho2` after it, the skip over the run
+// for an invalid ray.  Only where a direction STOPS depends on the best distance so far, and which direction goes
+// next depends on the last distance of each.  So the warp looks at 32 consecutive indices of a direction at once
+// (a window: lane k has index base + k*dir): every lane loads its ref point and computes its distance and its hop,
+// pointer doubling over the hops marks the lanes the walk really visits, a prefix minimum over those gives each
+// probe the best distance it would have seen, and ballots find the first lane where something happens.  All
+// decisions are the sequential loop's, on the same operands: strict `<` for the best (the earliest probe keeps a tie),
+// the stop test after the probe's own distance has been taken in.
+struct RayU {  // lane L's ray, warp-uniform
+    double wx, wy, rho2;
+    float phi;
+    int start_cell;
+};
+
+struct Win {
+    double d;       // own lane: squared distance (INF unless visited and valid)
+    double pm;      // own lane: minimum of d over the lanes up to and including this one
+    double rr2, cross2;  // own lane: operands of the stop test
+    int my;         // own lane: ref index
+    int next;       // own lane: my + hop
+    bool beyond;    // own lane: past the start cell in the walking direction (the stop test applies)
+    bool wide;      // own lane: dtheta > pi/2 (the stop test is rho2 > best)
+    unsigned visited, validm, oobm;  // uniform: lanes the walk visits / of those, valid rays / beyond the scan's end
+    int exit_idx;   // uniform: where the walk goes after its last visited lane
+};
+
+__device__ __forceinline__ Win load_window(const WalkCtx &c, const RayU &u, int base, int sdir) {
+    const unsigned FULL = 0xffffffffu;
+    const float HALF_PI_F = 1.57079632679489662f;
+    const int lane = threadIdx.x & 31;
+    const int to = c.n - 1;
+    const unsigned a_jt = sdir > 0 ? c.jt : c.jt + 4u * (unsigned)c.n;
+    Win w;
+    w.my = base + sdir * lane;
+    const bool inb = (unsigned)w.my <= (unsigned)to;
+    double2 q = make_double2(0.0, 0.0);
+    int hops = 0;
+    w.rr2 = -1.0;
+    if (inb) {
+        w.rr2 = lds_f64(c.rr2 + 8u * w.my);
+        q = lds_f64x2(c.refp + 16u * w.my);
+        hops = lds_b32(a_jt + 4u * w.my);
     }
-    *j2out = j2;
-    return j1;
+    const bool valid = inb && w.rr2 >= 0;
+    w.beyond = (w.my - u.start_cell) * sdir > 0;
+    int hop = hops >> 16;  // an invalid ref ray: the skip over its whole run
+    if (valid) hop = w.beyond ? (w.rr2 < u.rho2 ? (int)(short)hops : (hops >> 16)) : sdir;
+    w.next = w.my + hop;
+    int nx = inb ? lane + hop * sdir : 32;
+    nx = nx > 32 ? 32 : nx;
+    unsigned R = 1u;
+#pragma unroll
+    for (int k = 0; k < 5; k++) {
+        const unsigned add = ((R >> lane) & 1u) && nx < 32 ? (1u << nx) : 0u;
+        R |= __reduce_or_sync(FULL, add);
+        const int nx2 = __shfl_sync(FULL, nx, nx & 31);
+        nx = nx < 32 ? nx2 : 32;
+    }
+    w.visited = R;
+    const bool vis = (R >> lane) & 1u;
+    w.validm = __ballot_sync(FULL, vis && valid);
+    w.oobm = __ballot_sync(FULL, vis && !inb);
+    w.d = (vis && valid) ? dist2(u.wx, u.wy, q.x, q.y) : INFINITY;
+    w.pm = w.d;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const double v = __shfl_up_sync(FULL, w.pm, o);
+        if (lane >= o) w.pm = v < w.pm ? v : w.pm;
+    }
+    const float dth = theta_f(c.fi_min, c.dfi, w.my) - u.phi;
+    w.wide = (sdir > 0 ? dth : -dth) > HALF_PI_F;
+    const double cross = u.wx * q.y - u.wy * q.x;
+    w.cross2 = cross * cross;
+    w.exit_idx = __shfl_sync(FULL, w.next, 31 - __clz(R));
+    return w;
+}
+
+// own lane: does the stop test fire when the best distance is `best` at this probe?
+__device__ __forceinline__ bool win_stop(const Win &w, const RayU &u, int lane, double best) {
+    if (!((w.validm >> lane) & 1u) || !w.beyond) return false;
+    const double bi = w.pm < best ? w.pm : best;
+    return w.wide ? (u.rho2 > bi) : (w.cross2 > bi * w.rr2);
+}
+
+// take the lanes [from .. last] of a window into (cb, cj)
+__device__ __forceinline__ void win_take(const Win &w, int lane, int from, int last, double &cb, int &cj) {
+    const unsigned FULL = 0xffffffffu;
+    const double nb = __shfl_sync(FULL, w.pm, last);
+    const unsigned holders = __ballot_sync(FULL, w.d == nb && lane >= from && lane <= last);
+    if (nb < cb && holders) {
+        cb = nb;
+        cj = __shfl_sync(FULL, w.my, __ffs(holders) - 1);
+    }
+}
+
+// One direction alone, from idx, until it stops or leaves the scan.
+__device__ __forceinline__ void chain_one(const WalkCtx &c, const RayU &u, int idx, int sdir, double &cb, int &cj) {
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const int to = c.n - 1;
+#pragma unroll 1
+    while ((unsigned)idx <= (unsigned)to) {
+        const Win w = load_window(c, u, idx, sdir);
+        const unsigned ends = __ballot_sync(FULL, win_stop(w, u, lane, cb)) | w.oobm;
+        const int last = ends ? __ffs(ends) - 1 : 31;
+        win_take(w, lane, 0, last, cb, cj);
+        if (ends) break;
+        idx = w.exit_idx;
+    }
+}
+
+static __device__ __noinline__ void walk_warp_one(const WalkCtx c, int L, const Ray r, WalkState *st) {
+    const unsigned FULL = 0xffffffffu;
+    RayU u;
+    u.wx = __shfl_sync(FULL, r.wx, L); u.wy = __shfl_sync(FULL, r.wy, L); u.rho2 = __shfl_sync(FULL, r.rho2, L);
+    u.phi = __shfl_sync(FULL, r.phi, L); u.start_cell = __shfl_sync(FULL, r.start_cell, L);
+    double cb = __shfl_sync(FULL, st->best, L);
+    int cj = __shfl_sync(FULL, st->j1, L);
+    chain_one(c, u, __shfl_sync(FULL, st->up, L), __shfl_sync(FULL, st->dir, L), cb, cj);
+    if ((int)(threadIdx.x & 31) == L) { st->best = cb; st->j1 = cj; st->dir = 0; }
+}
+
+// Both directions alive.  The sequential loop probes upwards while last_up < last_down and downwards otherwise, so
+// it moves in RUNS: an upward run ends with the first valid probe whose distance is not below last_down, a downward
+// run with the first whose distance is above last_up.  A run is a stretch of one window: its end is a ballot, the
+// stop tests inside it see min(best before the run, prefix minimum), and the first of {run end, stop, end of the
+// scan} decides how it goes on: with the other direction, with the other direction alone (chain_one), or with the
+// next window of the same direction.
+static __device__ __noinline__ void walk_warp_both(const WalkCtx c, int L, const Ray r, WalkState *st) {
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    RayU u;
+    u.wx = __shfl_sync(FULL, r.wx, L); u.wy = __shfl_sync(FULL, r.wy, L); u.rho2 = __shfl_sync(FULL, r.rho2, L);
+    u.phi = __shfl_sync(FULL, r.phi, L); u.start_cell = __shfl_sync(FULL, r.start_cell, L);
+    double cb = __shfl_sync(FULL, st->best, L);
+    int cj = __shfl_sync(FULL, st->j1, L);
+    double last[2] = {__shfl_sync(FULL, st->last_down, L), __shfl_sync(FULL, st->last_up, L)};  // [0] down, [1] up
+    int nextidx[2] = {__shfl_sync(FULL, st->down, L), __shfl_sync(FULL, st->up, L)};
+    const int to = c.n - 1;
+    Win W[2];
+    int pos[2] = {32, 32};  // next lane to take in each window; 32: the window has to be loaded (from nextidx)
+    int alone = -1;         // the direction that goes on alone once the other has ended
+#pragma unroll 1
+    for (;;) {
+        const int s = last[1] < last[0] ? 1 : 0;  // 1: upwards
+        const int sdir = s ? 1 : -1;
+        if (pos[s] == 32) {
+            if ((unsigned)nextidx[s] > (unsigned)to) { alone = s ^ 1; break; }  // ran off the scan: this side has ended
+            if (s) W[1] = load_window(c, u, nextidx[1], +1); else W[0] = load_window(c, u, nextidx[0], -1);
+            pos[s] = 0;
+        }
+        const Win &w = s ? W[1] : W[0];
+        const int from = pos[s];
+        const unsigned ge = FULL << from;
+        const double thr = last[s ^ 1];
+        const bool mine_valid = (w.validm >> lane) & 1u;
+        const unsigned endm = __ballot_sync(FULL, mine_valid && (s ? !(w.d < thr) : (thr < w.d))) & ge;
+        const unsigned stopm = __ballot_sync(FULL, win_stop(w, u, lane, cb)) & ge;
+        const unsigned oobm = w.oobm & ge;
+        const int e_run = endm ? __ffs(endm) - 1 : 32, e_stop = stopm ? __ffs(stopm) - 1 : 32;
+        const int e_oob = oobm ? __ffs(oobm) - 1 : 32;
+        if (e_oob < e_run && e_oob < e_stop) {  // the visited lanes before the end of the scan, then this side has ended
+            if (e_oob > from) win_take(w, lane, from, e_oob - 1, cb, cj);
+            alone = s ^ 1;
+            break;
+        }
+        if (e_stop <= e_run && e_stop < 32) {  // a stop test fired (its probe counts): this side has ended
+            win_take(w, lane, from, e_stop, cb, cj);
+            alone = s ^ 1;
+            break;
+        }
+        if (e_run < 32) {  // the run ends inside the window: the other direction goes next
+            win_take(w, lane, from, e_run, cb, cj);
+            last[s] = __shfl_sync(FULL, w.d, e_run);
+            const unsigned rest = w.visited & ~((2u << e_run) - 1u);
+            if (rest) pos[s] = __ffs(rest) - 1;
+            else { pos[s] = 32; nextidx[s] = w.exit_idx; }
+            continue;
+        }
+        // the run takes the rest of the window and goes on in the next one
+        win_take(w, lane, from, 31, cb, cj);
+        const unsigned took = w.validm & ge;
+        if (took) last[s] = __shfl_sync(FULL, w.d, 31 - __clz(took));
+        pos[s] = 32;
+        nextidx[s] = w.exit_idx;
+        (void)sdir;
+    }
+    // one direction is left: from where it stands, alone
+    {
+        const int idx = pos[alone] < 32 ? __shfl_sync(FULL, (alone ? W[1].my : W[0].my), pos[alone]) : nextidx[alone];
+        chain_one(c, u, idx, alone ? 1 : -1, cb, cj);
+    }
+    if (lane == L) { st->best = cb; st->j1 = cj; st->dir = 0; }
 }
 
 }  // namespace plicp2

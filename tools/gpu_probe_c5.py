@@ -45,6 +45,7 @@ print(f"C5: {P} pairs x {G} starts = {P*G} matches (n={n}) in {dt*1e3:.1f} ms (k
 print(f"    valid starts {r['valid'].mean():.3f}; iterations/start {r['iterations'].mean():.1f}; pairs with best start within 2 cm / 0.5 deg of truth: "
       f"{ok.mean():.4f} (any start: {ok_any.any(1).mean():.4f}; single start nearest odometry: {ok_any[:, 0].mean():.4f})")
 w = r["reserved"].astype(np.float64)
+print(f"    digest: hash-sum {int(r['corr_hash'].astype(np.uint64).sum())} iterations-sum {int(r['iterations'].sum())} x-sum {r['x'][r['valid'] == 1].sum():.15e}")
 print(f"    walks per start: {w[..., 0].mean():.0f} executed for {w[..., 1].mean():.0f} sequential ({w[..., 0].sum() / w[..., 1].sum():.2f}x); "
       f"re-search warp rounds {w[..., 2].mean():.0f}; kernel {kms / (P * G) * 148 * 1e3:.0f} us of SM time per start")
 if os.environ.get("ZHSM_LIB_VARIANT") == "timing":  # per-phase cycle counters instead of the result (tools/gpu_probe_phases.py)
