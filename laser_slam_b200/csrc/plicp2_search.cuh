@@ -103,8 +103,14 @@ __device__ __forceinline__ int walk_finish(const WalkCtx &c, double wx, double w
 }
 
 constexpr int WALK_BUDGET = 12;    // probes of the general loop before a walk with one side ended leaves it
-constexpr int BOTH_AFTER = 28;     // COOP: further probes with both sides alive before the warp takes the walk over
-constexpr int SOLO_BUDGET = 24;    // COOP: probes of the one-direction loop before the warp takes the walk over
+#ifndef PLICP_BOTH_AFTER
+#define PLICP_BOTH_AFTER 60
+#endif
+#ifndef PLICP_SOLO_BUDGET
+#define PLICP_SOLO_BUDGET 60
+#endif
+constexpr int BOTH_AFTER = PLICP_BOTH_AFTER;     // COOP: further probes with both sides alive before the warp takes the walk over
+constexpr int SOLO_BUDGET = PLICP_SOLO_BUDGET;    // COOP: probes of the one-direction loop before the warp takes the walk over
 constexpr int WALK_PENDING = -2;   // COOP: tricks_one returns this when the walk goes on with the whole warp
 
 // COOP (the instances for long scans, T >= 256): a walk that is still running after the budgets above is not
