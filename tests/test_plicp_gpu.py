@@ -193,3 +193,36 @@ def test_plicp_independent_of_cta_shape(threads):
     assert (pose_close(res["x"], g["plicp_x"][:300]) | ~both).mean() >= 0.995
     assert (res["iterations"] == g["plicp_iterations"][:300]).mean() >= 0.995
     assert ((res["corr_hash"] == g["plicp_hash"][:300]) | ~both).mean() >= 0.995
+
+
+def test_plicp_long_scans_poor_guesses_match_oracle():
+    """SURVEY 8d C5 in small: 2048-beam 360-degree scans, 16 first guesses per pair up to 0.3 m / 10 degrees off a noisy
+    odometry.  With such guesses one walk in twelve runs for hundreds of probes and some cross the whole scan; the
+    256-thread instance hands those to the warp (walk_warp_one / walk_warp_both, plicp2_search.cuh), which has to take
+    the sequential walk's decisions: pose, iterations and correspondence hash equal to the CPU restatement's."""
+    import torch
+    import laser_slam_b200 as zh
+    from oracle import pyoracle as po
+    P, G, n = 24, 16, 2048
+    PM_PI = 3.141592654
+    lz = zh.Laser()
+    lz.n = n; lz.fi_min = np.float32(-PM_PI); lz.dfi = np.float32((360 * PM_PI / 180) / (n - 1.0))
+    lz.min_range_cm = 10; lz.max_range_cm = 3000; lz.min_valid_points = n // 5; lz.scan_window = n // 10
+    eng = zh.Engine(0)
+    eng.set_laser(lz)
+    dev = torch.device("cuda:0")
+    d_scans = torch.empty((2 * P, n), dtype=torch.float32, device=dev)
+    d_truth = torch.empty((P, 3), dtype=torch.float64, device=dev)
+    eng.synth_pairs(d_scans, d_truth, 0, P, dmax_xy_m=0.5, dmax_th_rad=np.deg2rad(20.0), seed=20261105)
+    eng.median_filter(d_scans); eng.sync()
+    scans = d_scans.cpu().numpy(); tr = d_truth.cpu().numpy()
+    rng = np.random.default_rng(7)
+    odo = tr + rng.normal(0, 1, (P, 3)) * [0.1, 0.1, np.deg2rad(3.0)]
+    grid = np.array([[dx, dy, np.deg2rad(dt)] for dx in (-0.3, 0.3) for dy in (-0.3, 0.3) for dt in (-10, -3.3, 3.3, 10)])
+    guess = (odo[:, None, :] + grid[None]).reshape(-1, 3)
+    ri = np.repeat(np.arange(P, dtype=np.int32) * 2, G); si = ri + 1
+    res, _, _ = eng.plicp(scans, ri, si, first_guess=guess, want_corr=True)
+    eng.close()
+    o = po.zhcsm_fmatch_batch(scans, ri, si, lz.fi_min, lz.dfi, 10, 3000, first_guess=guess, nthreads=8)
+    _assert_same_as_oracle(res, o, min_frac=0.995)
+    assert (res["valid"] == 1).mean() > 0.9
