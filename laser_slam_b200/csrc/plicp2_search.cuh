@@ -13,6 +13,10 @@
 //     cross^2 > best_dist * |ref_j|^2         (or rho^2 > best_dist when dtheta > pi/2)
 // which needs 4 multiplications instead of a double-precision sin().  `rr < rho` (the jump-table choice) is
 // evaluated on the squares.  Both rewrites change the result only when a comparison is tied to ~1e-16 relative.
+//
+// Contents: make_ray (world point + start cell of a sens ray), walk_finish (validity rules + j2), tricks_one (one
+// ray's walk by its own lane), and -- for the long-scan instances (COOP, T >= 256) -- the warp-wide continuation of
+// walks that run for hundreds of probes (load_window, chain_one, walk_warp_one, walk_warp_both).
 #pragma once
 #include "plicp2_common.cuh"
 
