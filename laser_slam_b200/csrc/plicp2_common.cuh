@@ -10,6 +10,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <math.h>
+#include <stddef.h>
 #include <stdint.h>
 
 #include "zhsm_internal.h"
@@ -33,6 +34,7 @@ struct Ctl {
     int qn[2];          // re-search queue length (ping-pong over verify rounds)
     int topbyte;        // radix select: guessed top byte of the trim keys (that of the last result)
     int sel_below;      // radix select: keys whose top byte is below the guess
+    int npend;          // walks on the list of unfinished walks (plicp2_search.cuh)
 };
 
 // byte offsets into the dynamic shared memory block

@@ -46,14 +46,16 @@ struct IterCtx {
 #define STATS_ARG
 #endif
 
-// search sens ray i with its speculated last_best; returns true when it got a correspondence
-template <bool COOP>
-__device__ __forceinline__ bool search_ray(const Lay &l, const WalkCtx &w, const IterCtx &it, int i STATS_PARAM) {
+// search sens ray i with its speculated last_best; returns false when the walk went on the list of unfinished walks
+// (process_pending finishes it and writes cj1 / cj2 then)
+template <bool LIST>
+__device__ __forceinline__ bool search_ray(const Lay &l, const WalkCtx &w, const IterCtx &it,
+                                           const PendRef<LIST> &pr, int i STATS_PARAM) {
     const Ray ray = make_ray(sens_point(PL_SH(const float, l.sensr), it.cs2, i), it.x0, it.x1, it.cs, it.sn, it.min_theta, it.C1);
     int j2 = -1;
 #ifdef PLICP_WALK_STATS
     int trips = 0;
-    const int j1 = tricks_one<false>(w, ray, (int)PL_SH(const short, l.spec)[i], &j2, nullptr, &trips);
+    const int j1 = tricks_one<LIST>(w, ray, (int)PL_SH(const short, l.spec)[i], &j2, pr, i, &trips);
     const int fast = trips >> 16;
     trips &= 0xffff;
     g_stats[0] += trips;
@@ -63,50 +65,70 @@ __device__ __forceinline__ bool search_ray(const Lay &l, const WalkCtx &w, const
     g_stats[4] += trips > 32 ? fast : 0;
     g_stats[5] = trips > g_stats[5] ? trips : g_stats[5];
 #else
-    const int j1 = tricks_one<false>(w, ray, (int)PL_SH(const short, l.spec)[i], &j2, nullptr);
+    const int j1 = tricks_one<LIST>(w, ray, (int)PL_SH(const short, l.spec)[i], &j2, pr, i);
 #endif
+    if constexpr (LIST) {
+        if (j1 == WALK_PENDING) return false;
+    }
     PL_SH(short, l.cj1)[i] = (short)j1;
     PL_SH(short, l.cj2)[i] = (short)(j1 >= 0 ? j2 : -1);
-    return j1 >= 0;
+    return true;
 }
 
-// COOP instances (long scans): search_ray_coop is called by ALL lanes of a warp (active = this lane has a ray).  Each
-// lane walks its own ray; the few walks that would keep a single lane busy for hundreds of probes come back
-// WALK_PENDING and are finished by the whole warp, one after the other (walk_warp_one / walk_warp_both).
-static __device__ __noinline__ void finish_pending(const Lay l, const WalkCtx w, const IterCtx it, int i, bool mine,
-                                                   WalkState *st, int *j1, int *j2) {
-    const unsigned FULL = 0xffffffffu;
-    Ray ray = {0.0, 0.0, 0.0, 0.0f, 0};
-    if (mine) ray = make_ray(sens_point(PL_SH(const float, l.sensr), it.cs2, i), it.x0, it.x1, it.cs, it.sn, it.min_theta, it.C1);
-    unsigned pend = __ballot_sync(FULL, mine);
-    while (pend) {
-        const int L = __ffs(pend) - 1;
-        pend &= pend - 1;
-        if (__shfl_sync(FULL, st->dir, L) == 2) walk_warp_both(w, L, ray, st);
-        else walk_warp_one(w, L, ray, st);
-    }
-    if (mine) *j1 = walk_finish(w, ray.wx, ray.wy, st->j1, st->best, j2);
+// The walks a round left unfinished (tricks_one put them on the list), finished warp-wide: entry e by warp e mod NW.
+// Called by every thread after the barrier that ends the round; returns whether a finished walk changed its ray's j1.
+// Ends with a barrier when there was anything on the list.
+template <int T>
+static __device__ __noinline__ int finish_unfinished(const Lay l, const WalkCtx w, const IterCtx it,
+                                                     const PendRef<true> pr, int np);
+
+template <int T>
+__device__ __forceinline__ int process_pending(const Lay &l, const WalkCtx &w, const IterCtx &it,
+                                               const PendRef<(T >= 256)> &pr) {
+    if constexpr (T < 256) {
+        return 0;  // the list exists in the long-scan instances only
+    } else {
+        const int np = PL_SH(Ctl, l.ctl)->npend;
+        if (np == 0) return 0;
+        return finish_unfinished<T>(l, w, it, pr, np);
+    }  // rare: kept out of line, away from the callers' registers
 }
 
-__device__ __forceinline__ void search_ray_coop(const Lay &l, const WalkCtx &w, const IterCtx &it, int i, bool active STATS_PARAM) {
-    int j1 = -1, j2 = -1;
-    WalkState st;
-    st.dir = 0;
-    if (active) {
+template <int T>
+static __device__ __noinline__ int finish_unfinished(const Lay l, const WalkCtx w, const IterCtx it,
+                                                     const PendRef<true> pr, int np) {
+    constexpr int NW = T / 32;
+    Ctl *ctl = PL_SH(Ctl, l.ctl);
+    np = np < pr.pend_cap ? np : pr.pend_cap;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int changed = 0;
+#pragma unroll 1
+    for (int e = warp; e < np; e += NW) {
+        const unsigned a = pr.pend + 48u * (unsigned)e;
+        const double2 bl = lds_f64x2(a);
+        const double last_down = lds_f64(a + 16u);
+        int i, j1, up, down, dir, pad;
+        asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(i), "=r"(j1) : "r"(a + 24u));
+        asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(up), "=r"(down), "=r"(dir), "=r"(pad) : "r"(a + 32u));
         const Ray ray = make_ray(sens_point(PL_SH(const float, l.sensr), it.cs2, i), it.x0, it.x1, it.cs, it.sn, it.min_theta, it.C1);
-#ifdef PLICP_WALK_STATS
-        int trips = 0;
-        j1 = tricks_one<true>(w, ray, (int)PL_SH(const short, l.spec)[i], &j2, &st, &trips);
-        g_stats[0] += trips & 0xffff;
-#else
-        j1 = tricks_one<true>(w, ray, (int)PL_SH(const short, l.spec)[i], &j2, &st);
-#endif
+        RayU u;
+        u.wx = ray.wx; u.wy = ray.wy; u.rho2 = ray.rho2; u.phi = ray.phi; u.start_cell = ray.start_cell;
+        double cb = bl.x;
+        int cj = j1;
+        if (dir == 2) walk_warp_both(w, u, up, down, bl.y, last_down, &cb, &cj);
+        else walk_warp_one(w, u, up, dir, &cb, &cj);
+        int j2 = -1;
+        const int r1 = walk_finish(w, ray.wx, ray.wy, cj, cb, &j2);
+        if (lane == 0) {
+            short *cj1 = PL_SH(short, l.cj1);
+            changed |= (int)cj1[i] != r1;
+            cj1[i] = (short)r1;
+            PL_SH(short, l.cj2)[i] = (short)(r1 >= 0 ? j2 : -1);
+        }
     }
-    if (__any_sync(0xffffffffu, j1 == WALK_PENDING)) finish_pending(l, w, it, i, j1 == WALK_PENDING, &st, &j1, &j2);
-    if (active) {
-        PL_SH(short, l.cj1)[i] = (short)j1;
-        PL_SH(short, l.cj2)[i] = (short)(j1 >= 0 ? j2 : -1);
-    }
+    __syncthreads();
+    if (threadIdx.x == 0) ctl->npend = 0;  // the next round of walks is at least one more barrier away
+    return changed;
 }
 
 // find_correspondences_tricks for the whole scan: speculate / verify / re-search until the sequential result.
@@ -120,10 +142,10 @@ __device__ __forceinline__ void search_ray_coop(const Lay &l, const WalkCtx &w, 
 // sens: bit k = ray k*T+t exists and is valid; returns the mask of those rays holding a correspondence.
 template <int T>
 __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const WalkCtx &w, const IterCtx &it, int C,
-                                                         unsigned sens, bool chunked, const uint2 *jt_src, WalkDiag &dg,
+                                                         unsigned sens, bool chunked, const uint2 *jt_src,
+                                                         const PendRef<(T >= 256)> &pr, WalkDiag &dg,
                                                          PhaseClock &pc STATS_PARAM) {
     constexpr int NW = T / 32;
-    constexpr bool COOP = T >= 256;  // long scans: long walks are finished by the warp (plicp2_search.cuh)
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int n = w.n;
     const unsigned lane_lt = (1u << lane) - 1u;
@@ -138,18 +160,12 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
     }
     if (!chunked) {
 #pragma unroll 1
-        for (int k = 0; k < C; k++) {
-            if constexpr (COOP) {
-                const bool act = sens >> k & 1u;
-                dg.walks += act;
-                dg.first += act;
-                search_ray_coop(l, w, it, k * T + t, act STATS_ARG);
-            } else if (sens >> k & 1u) {
+        for (int k = 0; k < C; k++)
+            if (sens >> k & 1u) {
                 dg.walks++;
                 dg.first++;
-                search_ray<false>(l, w, it, k * T + t STATS_ARG);
+                search_ray<(T >= 256)>(l, w, it, pr, k * T + t STATS_ARG);
             }
-        }
     } else {
         // thread t walks the rays [t*C, (t+1)*C) in order and hands last_best from one to the next: only the first
         // ray of a chunk is speculated
@@ -158,38 +174,25 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
         const short *cj1r = PL_SH(const short, l.cj1);
         int lb = 0;
         bool have = false;
-        if constexpr (COOP) {
 #pragma unroll 1
-            for (int q = 0; q < C; q++) {
-                const int i = t * C + q;
-                const bool act = i < n && !(sensr[i < n ? i : 0] < 0);  // an invalid sens ray: no walk, last_best unchanged
-                if (act && have) specw[i] = (short)lb;
-                dg.walks += act;
-                dg.first += act;
-                search_ray_coop(l, w, it, i, act STATS_ARG);
-                if (act) {
-                    const int c1 = cj1r[i];
-                    lb = c1 >= 0 ? c1 : (int)specw[i];
-                    have = true;
-                }
-            }
-        } else {
-#pragma unroll 1
-            for (int q = 0; q < C; q++) {
-                const int i = t * C + q;
-                if (i >= n) break;
-                if (sensr[i] < 0) continue;  // invalid sens ray: no walk, last_best unchanged
-                if (have) specw[i] = (short)lb;
-                dg.walks++;
-                dg.first++;
-                search_ray<false>(l, w, it, i STATS_ARG);
+        for (int q = 0; q < C; q++) {
+            const int i = t * C + q;
+            if (i >= n) break;
+            if (sensr[i] < 0) continue;  // invalid sens ray: no walk, last_best unchanged
+            if (have) specw[i] = (short)lb;
+            dg.walks++;
+            dg.first++;
+            if (search_ray<(T >= 256)>(l, w, it, pr, i STATS_ARG)) {
                 const int c1 = cj1r[i];
                 lb = c1 >= 0 ? c1 : (int)specw[i];
                 have = true;
+            } else {
+                have = false;  // an unfinished walk: its successor is speculated like the first ray of a chunk
             }
         }
     }
     __syncthreads();
+    process_pending<T>(l, w, it, pr);
     pc.mark(2);
     short *cj1 = PL_SH(short, l.cj1);
     short *spec = PL_SH(short, l.spec);
@@ -237,28 +240,21 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
         const int total = *qn;
         if (total == 0) break;
         dg.rounds++;
-        int changed = 0;
-        if constexpr (COOP) {
+        int changed = 0, unfinished = 0;
 #pragma unroll 1
-            for (int e = t; e - lane < total; e += T) {  // whole warps: the COOP search is a warp-wide call
-                const bool act = e < total;
-                const int i = act ? (int)queue[e] : 0;
-                const int before = cj1[i];
-                dg.walks += act;
-                search_ray_coop(l, w, it, i, act STATS_ARG);
-                changed |= act && (int)cj1[i] != before;
-            }
-        } else {
-#pragma unroll 1
-            for (int e = t; e < total; e += T) {
-                const int i = (int)queue[e];
-                const int before = cj1[i];
-                dg.walks++;
-                search_ray<false>(l, w, it, i STATS_ARG);
-                changed |= (int)cj1[i] != before;
-            }
+        for (int e = t; e < total; e += T) {
+            const int i = (int)queue[e];
+            const int before = cj1[i];
+            dg.walks++;
+            if (search_ray<(T >= 256)>(l, w, it, pr, i STATS_ARG)) changed |= (int)cj1[i] != before;
+            else unfinished = 1;  // on the list: process_pending says whether its j1 changed
         }
-        if (!__syncthreads_or(changed)) break;  // last_best of every ray is what it was walked with
+        // the usual end: nothing changed and nothing is unfinished -- last_best of every ray is what it was walked with
+        if (!__syncthreads_or(changed | unfinished)) break;
+        if constexpr (T >= 256) {
+            changed |= process_pending<T>(l, w, it, pr);
+            if (!__syncthreads_or(changed)) break;
+        }
     }
     pc.mark(3);
     unsigned valid = 0;
@@ -320,6 +316,7 @@ __global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 2 : 1)) plicp2_k
     }
     if (t == 0) {
         ctl->topbyte = 0x3f;
+        ctl->npend = 0;
         for (int k = 0; k < 3; k++) ctl->x[0][k] = a.first_guess ? a.first_guess[3 * (size_t)job + k] : 0.0;
         ctl->cs[0] = cos(ctl->x[0][2]);
         ctl->sn[0] = sin(ctl->x[0][2]);
@@ -355,6 +352,16 @@ __global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 2 : 1)) plicp2_k
         wc.refp = sb + l.refp; wc.rr2 = sb + l.rr2; wc.jt = sb + l.jt;
     }
     wc.n = n; wc.fi_min = L.fi_min; wc.dfi = L.dfi;
+    PendRef<(T >= 256)> pr;
+    if constexpr (T >= 256) {
+        // the list of unfinished walks lies in the d2j area above the search's queue and group table
+        const unsigned sb = (unsigned)__cvta_generic_to_shared(smem_raw);
+        const unsigned lo = (sb + l.d2j + 2u * (unsigned)(n + C * NW) + 15u) & ~15u, hi = sb + l.d2j + 8u * (unsigned)n;
+        pr.pend = lo;
+        pr.npend = sb + l.ctl + (unsigned)offsetof(Ctl, npend);
+        const int room = hi > lo ? (int)((hi - lo) / 48u) : 0;
+        pr.pend_cap = room < 1024 ? room : 1024;
+    }
     wc.maxd2 = P.max_correspondence_dist * P.max_correspondence_dist;
     const int max_it = P.max_iterations < ZHSM_MAX_ITER ? P.max_iterations : ZHSM_MAX_ITER;
     const double fail_perc = 0.05;
@@ -378,7 +385,7 @@ __global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 2 : 1)) plicp2_k
             it.cs = ctl->cs[par];
             it.sn = ctl->sn[par];
             if (t == 0) ctl->hash_acc[iteration & 1] = 0;
-            valid = find_correspondences<T>(l, wc, it, C, sens, iteration < a.chunk_iters, jt_src, dg, pc STATS_ARG);
+            valid = find_correspondences<T>(l, wc, it, C, sens, iteration < a.chunk_iters, jt_src, pr, dg, pc STATS_ARG);
             if (P.outliers_remove_doubles) {
                 for (int j = t; j < n; j += T) d2j[j] = BIG;  // the search used this area as its queue
                 __syncthreads();
@@ -636,7 +643,7 @@ __global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 2 : 1)) plicp2_k
         it.cs = ctl->cs[0];
         it.sn = ctl->sn[0];
         // "recompute correspondences in case of restarts" (icp.c): world coords at best x + tricks, no outlier pass
-        if (v_restarted) valid = find_correspondences<T>(l, wc, it, C, sens, a.chunk_iters > 0, jt_src, dg, pc STATS_ARG);
+        if (v_restarted) valid = find_correspondences<T>(l, wc, it, C, sens, a.chunk_iters > 0, jt_src, pr, dg, pc STATS_ARG);
     }
     if (t == 0) ctl->hash_acc[0] = 0;
 #pragma unroll 1

@@ -15,7 +15,7 @@
 // evaluated on the squares.  Both rewrites change the result only when a comparison is tied to ~1e-16 relative.
 //
 // Contents: make_ray (world point + start cell of a sens ray), walk_finish (validity rules + j2), tricks_one (one
-// ray's walk by its own lane), and -- for the long-scan instances (COOP, T >= 256) -- the warp-wide continuation of
+// ray's walk by its own lane), and -- for the long-scan instances (LIST, T >= 256) -- the warp-wide continuation of
 // walks that run for hundreds of probes (load_window, chain_one, walk_warp_one, walk_warp_both).
 #pragma once
 #include "plicp2_common.cuh"
@@ -113,26 +113,51 @@ constexpr int WALK_BUDGET = 12;    // probes of the general loop before a walk w
 #ifndef PLICP_SOLO_BUDGET
 #define PLICP_SOLO_BUDGET 60
 #endif
-constexpr int BOTH_AFTER = PLICP_BOTH_AFTER;     // COOP: further probes with both sides alive before the warp takes the walk over
-constexpr int SOLO_BUDGET = PLICP_SOLO_BUDGET;    // COOP: probes of the one-direction loop before the warp takes the walk over
-constexpr int WALK_PENDING = -2;   // COOP: tricks_one returns this when the walk goes on with the whole warp
+constexpr int BOTH_AFTER = PLICP_BOTH_AFTER;     // LIST: further probes with both sides alive before the walk goes on the list
+constexpr int SOLO_BUDGET = PLICP_SOLO_BUDGET;    // LIST: probes of the one-direction loop before the walk goes on the list
+constexpr int WALK_PENDING = -2;   // tricks_one returns this when the walk has been put on the list
 
-// COOP (the instances for long scans, T >= 256): a walk that is still running after the budgets above is not
-// finished by its own lane -- hundreds of dependent probes while the rest of the CTA waits at the next barrier --
-// but handed to its warp (walk_warp_one / walk_warp_both below) in this state.
+// A walk that is still running after the budgets above is not finished by its own lane -- hundreds of dependent
+// probes while the rest of the CTA waits at the next barrier -- but put on a list in shared memory in this state.
+// After the barrier that ends the round of walks the warps take the list's entries in turn and finish each one
+// warp-wide (process_pending in plicp2_kernel.cuh, walk_warp_one / walk_warp_both below).  The common path pays
+// nothing for it: no warp-wide call protocol, one counter read per round.  A full list: the lane walks on.
 struct WalkState {
     double best, last_up, last_down;
+    int i;         // the sens ray
     int j1;
     int up, down;  // next index to probe in each direction (dir = +-1: `up` holds the one index)
     int dir;       // +1 / -1: one direction left; 2: both directions alive
+    int pad_;
+};
+static_assert(sizeof(WalkState) == 48, "WalkState is a 48-byte shared-memory record");
+
+// Where the list is: only the long-scan instances (LIST) have one, the others carry nothing around.
+template <bool LIST>
+struct PendRef {};
+template <>
+struct PendRef<true> {
+    unsigned pend, npend;  // shared-memory addresses of the list and of its counter
+    int pend_cap;          // entries the list can hold
 };
 
-// One ray's walk.  Returns j1 (a fully valid correspondence) or -1 and j2 in *j2out.
-// State: up / down = next index to probe in each direction; stopped bit 0 / 1 = that direction has ended.
-// CSM initialises last_dist_up = 0 and last_dist_down = -1; the only use is "last_up < last_down", false for both
-// (0, -1) and (0, 0), so 0 serves for both.
-template <bool COOP>
-static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int last_best, int *j2out, WalkState *out
+// reserve a list entry and write the state; false when the list is full
+__device__ __forceinline__ bool pend_push(const PendRef<false> &, const WalkState &) { return false; }
+__device__ __forceinline__ bool pend_push(const PendRef<true> &c, const WalkState &st) {
+    int slot;
+    asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(slot) : "r"(c.npend) : "memory");
+    if (slot >= c.pend_cap) return false;
+    const unsigned a = c.pend + 48u * (unsigned)slot;
+    asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(a), "d"(st.best), "d"(st.last_up) : "memory");
+    asm volatile("st.shared.f64 [%0], %1;" ::"r"(a + 16u), "d"(st.last_down) : "memory");
+    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(a + 24u), "r"(st.i), "r"(st.j1) : "memory");
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a + 32u), "r"(st.up), "r"(st.down), "r"(st.dir), "r"(0) : "memory");
+    return true;
+}
+
+template <bool LIST>
+static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int last_best, int *j2out,
+                                              const PendRef<LIST> pr, int ray_i
 #ifdef PLICP_WALK_STATS
                                               , int *trips_out
 #endif
@@ -158,6 +183,7 @@ static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int 
     // The general loop: the next probe goes where the last distance was smaller (or where the walk is still alive).
     // A walk that is still running after WALK_BUDGET probes with one direction ended leaves for the loop below.
     int budget = WALK_BUDGET;
+    bool ask = LIST;  // may this walk be put on the list?
 #pragma unroll 1
     while (stopped != 3) {
 #ifdef PLICP_WALK_STATS
@@ -165,13 +191,17 @@ static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int 
 #endif
         if (--budget < 0) {
             if (stopped != 0) break;
-            if (COOP && budget < -BOTH_AFTER) {
-                out->best = best; out->last_up = last_up; out->last_down = last_down;
-                out->j1 = j1; out->up = up; out->down = down; out->dir = 2;
+            if (LIST && budget < -BOTH_AFTER && ask) {
+                WalkState st;
+                st.best = best; st.last_up = last_up; st.last_down = last_down;
+                st.i = ray_i; st.j1 = j1; st.up = up; st.down = down; st.dir = 2;
+                if (pend_push(pr, st)) {
 #ifdef PLICP_WALK_STATS
-                g_walk_trips = trips;
+                    g_walk_trips = trips;
 #endif
-                return WALK_PENDING;
+                    return WALK_PENDING;
+                }
+                ask = false;
             }
         }
         const bool now_up = (stopped == 2) | ((stopped == 0) & (last_up < last_down));
@@ -229,13 +259,17 @@ static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int 
         int solo = SOLO_BUDGET;
 #pragma unroll 1
         while ((unsigned)idx <= (unsigned)to) {
-            if (COOP && --solo < 0) {
-                out->best = best; out->last_up = 0; out->last_down = 0;
-                out->j1 = j1; out->up = idx; out->down = 0; out->dir = sdir;
+            if (LIST && --solo < 0 && ask) {
+                WalkState st;
+                st.best = best; st.last_up = 0; st.last_down = 0;
+                st.i = ray_i; st.j1 = j1; st.up = idx; st.down = 0; st.dir = sdir;
+                if (pend_push(pr, st)) {
 #ifdef PLICP_WALK_STATS
-                g_walk_trips = trips;
+                    g_walk_trips = trips;
 #endif
-                return WALK_PENDING;
+                    return WALK_PENDING;
+                }
+                ask = false;
             }
 #ifdef PLICP_WALK_STATS
             trips += 0x10001;
@@ -272,7 +306,7 @@ static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int 
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// COOP: the rest of a long walk, run by all 32 lanes of the warp for ONE ray (lane L's; its data is broadcast).
+// LIST: the rest of a long walk, run by all 32 lanes of a warp for ONE ray (a list entry: all arguments uniform).
 //
 // The indices a direction probes do not depend on the distances found: from idx the walk goes to idx + hop(idx), hop
 // being a unit step before the start cell, a jump-table entry chosen by `rr2 < rho2` after it, the skip over the run
@@ -386,15 +420,13 @@ __device__ __forceinline__ void chain_one(const WalkCtx &c, const RayU &u, int i
     }
 }
 
-static __device__ __noinline__ void walk_warp_one(const WalkCtx c, int L, const Ray r, WalkState *st) {
-    const unsigned FULL = 0xffffffffu;
-    RayU u;
-    u.wx = __shfl_sync(FULL, r.wx, L); u.wy = __shfl_sync(FULL, r.wy, L); u.rho2 = __shfl_sync(FULL, r.rho2, L);
-    u.phi = __shfl_sync(FULL, r.phi, L); u.start_cell = __shfl_sync(FULL, r.start_cell, L);
-    double cb = __shfl_sync(FULL, st->best, L);
-    int cj = __shfl_sync(FULL, st->j1, L);
-    chain_one(c, u, __shfl_sync(FULL, st->up, L), __shfl_sync(FULL, st->dir, L), cb, cj);
-    if ((int)(threadIdx.x & 31) == L) { st->best = cb; st->j1 = cj; st->dir = 0; }
+// All arguments warp-uniform (a list entry and its ray); the result comes back in (cb, cj).
+static __device__ __noinline__ void walk_warp_one(const WalkCtx c, const RayU u, int idx, int sdir, double *cbp, int *cjp) {
+    double cb = *cbp;
+    int cj = *cjp;
+    chain_one(c, u, idx, sdir, cb, cj);
+    *cbp = cb;
+    *cjp = cj;
 }
 
 // Both directions alive.  The sequential loop probes upwards while last_up < last_down and downwards otherwise, so
@@ -403,16 +435,14 @@ static __device__ __noinline__ void walk_warp_one(const WalkCtx c, int L, const 
 // stop tests inside it see min(best before the run, prefix minimum), and the first of {run end, stop, end of the
 // scan} decides how it goes on: with the other direction, with the other direction alone (chain_one), or with the
 // next window of the same direction.
-static __device__ __noinline__ void walk_warp_both(const WalkCtx c, int L, const Ray r, WalkState *st) {
+static __device__ __noinline__ void walk_warp_both(const WalkCtx c, const RayU u, int up, int down, double last_up,
+                                                   double last_down, double *cbp, int *cjp) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
-    RayU u;
-    u.wx = __shfl_sync(FULL, r.wx, L); u.wy = __shfl_sync(FULL, r.wy, L); u.rho2 = __shfl_sync(FULL, r.rho2, L);
-    u.phi = __shfl_sync(FULL, r.phi, L); u.start_cell = __shfl_sync(FULL, r.start_cell, L);
-    double cb = __shfl_sync(FULL, st->best, L);
-    int cj = __shfl_sync(FULL, st->j1, L);
-    double last[2] = {__shfl_sync(FULL, st->last_down, L), __shfl_sync(FULL, st->last_up, L)};  // [0] down, [1] up
-    int nextidx[2] = {__shfl_sync(FULL, st->down, L), __shfl_sync(FULL, st->up, L)};
+    double cb = *cbp;
+    int cj = *cjp;
+    double last[2] = {last_down, last_up};  // [0] down, [1] up
+    int nextidx[2] = {down, up};
     const int to = c.n - 1;
     Win W[2];
     int pos[2] = {32, 32};  // next lane to take in each window; 32: the window has to be loaded (from nextidx)
@@ -467,7 +497,8 @@ static __device__ __noinline__ void walk_warp_both(const WalkCtx c, int L, const
         const int idx = pos[alone] < 32 ? __shfl_sync(FULL, (alone ? W[1].my : W[0].my), pos[alone]) : nextidx[alone];
         chain_one(c, u, idx, alone ? 1 : -1, cb, cj);
     }
-    if (lane == L) { st->best = cb; st->j1 = cj; st->dir = 0; }
+    *cbp = cb;
+    *cjp = cj;
 }
 
 }  // namespace plicp2
