@@ -335,7 +335,8 @@ struct Win {
     int exit_idx;   // uniform: where the walk goes after its last visited lane
 };
 
-__device__ __forceinline__ Win load_window(const WalkCtx &c, const RayU &u, int base, int sdir) {
+// cb: the best distance so far (it only falls afterwards)
+__device__ __forceinline__ Win load_window(const WalkCtx &c, const RayU &u, int base, int sdir, double cb) {
     const unsigned FULL = 0xffffffffu;
     const float HALF_PI_F = 1.57079632679489662f;
     const int lane = threadIdx.x & 31;
@@ -360,23 +361,33 @@ __device__ __forceinline__ Win load_window(const WalkCtx &c, const RayU &u, int 
     int nx = inb ? lane + hop * sdir : 32;
     nx = nx > 32 ? 32 : nx;
     unsigned R = 1u;
+    const unsigned inbm = __ballot_sync(FULL, inb);
+    if (__all_sync(FULL, !inb || nx == lane + 1)) {
+        // unit steps only (always so before the start cell): every ray of the window is visited, and the first index
+        // past the end of the scan if the window reaches it (the in-bounds lanes are a prefix)
+        R = inbm | (inbm + 1u);
+    } else {
 #pragma unroll
-    for (int k = 0; k < 5; k++) {
-        const unsigned add = ((R >> lane) & 1u) && nx < 32 ? (1u << nx) : 0u;
-        R |= __reduce_or_sync(FULL, add);
-        const int nx2 = __shfl_sync(FULL, nx, nx & 31);
-        nx = nx < 32 ? nx2 : 32;
+        for (int k = 0; k < 5; k++) {
+            const unsigned add = ((R >> lane) & 1u) && nx < 32 ? (1u << nx) : 0u;
+            R |= __reduce_or_sync(FULL, add);
+            const int nx2 = __shfl_sync(FULL, nx, nx & 31);
+            nx = nx < 32 ? nx2 : 32;
+        }
     }
     w.visited = R;
     const bool vis = (R >> lane) & 1u;
     w.validm = __ballot_sync(FULL, vis && valid);
     w.oobm = __ballot_sync(FULL, vis && !inb);
     w.d = (vis && valid) ? dist2(u.wx, u.wy, q.x, q.y) : INFINITY;
-    w.pm = w.d;
+    w.pm = INFINITY;
+    if (__any_sync(FULL, w.d < cb)) {  // else no probe of this window can ever lower the best: min(pm, best) = best
+        w.pm = w.d;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const double v = __shfl_up_sync(FULL, w.pm, o);
-        if (lane >= o) w.pm = v < w.pm ? v : w.pm;
+        for (int o = 1; o < 32; o <<= 1) {
+            const double v = __shfl_up_sync(FULL, w.pm, o);
+            if (lane >= o) w.pm = v < w.pm ? v : w.pm;
+        }
     }
     const float dth = theta_f(c.fi_min, c.dfi, w.my) - u.phi;
     w.wide = (sdir > 0 ? dth : -dth) > HALF_PI_F;
@@ -411,7 +422,7 @@ __device__ __forceinline__ void chain_one(const WalkCtx &c, const RayU &u, int i
     const int to = c.n - 1;
 #pragma unroll 1
     while ((unsigned)idx <= (unsigned)to) {
-        const Win w = load_window(c, u, idx, sdir);
+        const Win w = load_window(c, u, idx, sdir, cb);
         const unsigned ends = __ballot_sync(FULL, win_stop(w, u, lane, cb)) | w.oobm;
         const int last = ends ? __ffs(ends) - 1 : 31;
         win_take(w, lane, 0, last, cb, cj);
@@ -453,7 +464,7 @@ static __device__ __noinline__ void walk_warp_both(const WalkCtx c, const RayU u
         const int sdir = s ? 1 : -1;
         if (pos[s] == 32) {
             if ((unsigned)nextidx[s] > (unsigned)to) { alone = s ^ 1; break; }  // ran off the scan: this side has ended
-            if (s) W[1] = load_window(c, u, nextidx[1], +1); else W[0] = load_window(c, u, nextidx[0], -1);
+            if (s) W[1] = load_window(c, u, nextidx[1], +1, cb); else W[0] = load_window(c, u, nextidx[0], -1, cb);
             pos[s] = 0;
         }
         const Win &w = s ? W[1] : W[0];
