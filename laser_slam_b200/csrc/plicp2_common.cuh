@@ -35,6 +35,7 @@ struct Ctl {
     int topbyte;        // radix select: guessed top byte of the trim keys (that of the last result)
     int sel_below;      // radix select: keys whose top byte is below the guess
     int npend;          // walks on the list of unfinished walks (plicp2_search.cuh)
+    int pend_next;      // next list entry to be taken by a warp
 };
 
 // byte offsets into the dynamic shared memory block

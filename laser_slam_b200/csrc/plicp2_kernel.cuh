@@ -97,13 +97,17 @@ __device__ __forceinline__ int process_pending(const Lay &l, const WalkCtx &w, c
 template <int T>
 static __device__ __noinline__ int finish_unfinished(const Lay l, const WalkCtx w, const IterCtx it,
                                                      const PendRef<true> pr, int np) {
-    constexpr int NW = T / 32;
     Ctl *ctl = PL_SH(Ctl, l.ctl);
     np = np < pr.pend_cap ? np : pr.pend_cap;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
     int changed = 0;
+    // the walks differ in length by two orders of magnitude: a warp takes the next entry when it is done with its last
 #pragma unroll 1
-    for (int e = warp; e < np; e += NW) {
+    for (;;) {
+        int e = 0;
+        if (lane == 0) e = atomicAdd(&ctl->pend_next, 1);
+        e = __shfl_sync(0xffffffffu, e, 0);
+        if (e >= np) break;
         const unsigned a = pr.pend + 48u * (unsigned)e;
         const double2 bl = lds_f64x2(a);
         const double last_down = lds_f64(a + 16u);
@@ -127,7 +131,7 @@ static __device__ __noinline__ int finish_unfinished(const Lay l, const WalkCtx 
         }
     }
     __syncthreads();
-    if (threadIdx.x == 0) ctl->npend = 0;  // the next round of walks is at least one more barrier away
+    if (threadIdx.x == 0) { ctl->npend = 0; ctl->pend_next = 0; }  // the next round of walks is at least one more barrier away
     return changed;
 }
 
@@ -317,6 +321,7 @@ __global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 2 : 1)) plicp2_k
     if (t == 0) {
         ctl->topbyte = 0x3f;
         ctl->npend = 0;
+        ctl->pend_next = 0;
         for (int k = 0; k < 3; k++) ctl->x[0][k] = a.first_guess ? a.first_guess[3 * (size_t)job + k] : 0.0;
         ctl->cs[0] = cos(ctl->x[0][2]);
         ctl->sn[0] = sin(ctl->x[0][2]);
