@@ -108,10 +108,10 @@ __device__ __forceinline__ int walk_finish(const WalkCtx &c, double wx, double w
 
 constexpr int WALK_BUDGET = 12;    // probes of the general loop before a walk with one side ended leaves it
 #ifndef PLICP_BOTH_AFTER
-#define PLICP_BOTH_AFTER 60
+#define PLICP_BOTH_AFTER 100
 #endif
 #ifndef PLICP_SOLO_BUDGET
-#define PLICP_SOLO_BUDGET 60
+#define PLICP_SOLO_BUDGET 32
 #endif
 constexpr int BOTH_AFTER = PLICP_BOTH_AFTER;     // LIST: further probes with both sides alive before the walk goes on the list
 constexpr int SOLO_BUDGET = PLICP_SOLO_BUDGET;    // LIST: probes of the one-direction loop before the walk goes on the list
