@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libzhsm.so")
-SOURCES = ["zhsm_api.cu", "plicp2_dispatch.cu", "plicp2_t128.cu", "plicp2_t192.cu", "plicp2_t256.cu", "plicp2_t512.cu", "plicp2_jump.cu", "plicp2_debug.cu", "psm_sm100.cu", "zhsm_psm_api.cu", "icp_sm100.cu", "zhsm_icp_api.cu", "graph_sm100.cu", "submap_sm100.cu", "synth_sm100.cu"]
+SOURCES = ["zhsm_api.cu", "plicp2_dispatch.cu", "plicp2_t128.cu", "plicp2_t192.cu", "plicp2_t256.cu", "plicp2_t512.cu", "plicp2_jump.cu", "plicp2_debug.cu", "psm_sm100.cu", "zhsm_psm_api.cu", "icp_sm100.cu", "zhsm_icp_api.cu", "graph_sm100.cu", "submap_sm100.cu", "synth_sm100.cu", "csm_compat.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 # -fmad=false: the reference links an x86-64 (no FMA contraction) CSM; every a*b+c must round twice like it does
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-fmad=false",
@@ -27,6 +27,7 @@ def build(force=False, verbose=False, variant=None, defs=()):
     os.makedirs(objdir, exist_ok=True)
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))]
     headers.append(os.path.join(HERE, "..", "include", "zhsm.h"))
+    headers.append(os.path.join(HERE, "..", "include", "csm_compat.h"))
     ccbin = [] if not os.path.exists("/usr/bin/g++") else ["-ccbin", "/usr/bin/g++"]
     log = os.path.join(HERE, "build%s.log" % ("_" + variant if variant else ""))
     objs, rebuilt = [], False
@@ -85,6 +86,28 @@ def build_host(verbose=False):
             cmd = [cxx, "-O2", "-std=c++17", "-Wall", "-I" + os.path.join(root, "include"), "-I" + host, "-o", exe_k, src,
                    "-L" + HERE, "-lzhsm_host", "-lzhsm", "-Wl,-rpath," + HERE]
             subprocess.run(cmd, check=True)
+    # plain C against the CSM-shaped entry: includes <csm/csm_all.h>, links libzhsm.so only
+    cc = "/usr/bin/gcc" if os.path.exists("/usr/bin/gcc") else "gcc"
+    inc = os.path.join(root, "include")
+    exe_c = os.path.join(bdir, "csm_plain")
+    src_c = os.path.join(tdir, "csm_plain.c")
+    lib = os.path.join(HERE, "libzhsm.so")
+    if not os.path.exists(exe_c) or os.path.getmtime(exe_c) < newest([src_c, lib, os.path.join(inc, "csm_compat.h")]):
+        subprocess.run([cc, "-O2", "-std=gnu99", "-Wall", "-I" + inc, "-o", exe_c, src_c, "-L" + HERE, "-lzhsm",
+                        "-Wl,-rpath," + HERE], check=True)
+    # the REFERENCE'S OWN CCanonicalMatcher, compiled unmodified where it lies (never copied) against include/csm/*.h
+    # and linked against libzhsm.so instead of libcsm (only where /root/reference exists; the binary travels)
+    ref = os.environ.get("ZHSM_REFERENCE", "/root/reference")
+    ref_src = os.path.join(ref, "src", "zhcsm", "ZHCanonical_Matcher.cpp")
+    if os.path.exists(ref_src):
+        exe_r = os.path.join(bdir, "ref_zhcsm_on_zhsm")
+        drv = os.path.join(tdir, "ref_zhcsm_driver.cpp")
+        zhpsm = os.path.join(ref, "src", "zhpsm")
+        if not os.path.exists(exe_r) or os.path.getmtime(exe_r) < newest([drv, lib, ref_src, os.path.join(inc, "csm_compat.h")]):
+            subprocess.run([cxx, "-O2", "-w", "-I" + inc, "-I" + os.path.join(tdir, "stubs"), "-I" + zhpsm,
+                            "-I" + os.path.join(ref, "src", "zhcsm"), "-o", exe_r, drv, ref_src,
+                            os.path.join(zhpsm, "ZHPolar_Match.cpp"), os.path.join(zhpsm, "point.cpp"),
+                            "-L" + HERE, "-lzhsm", "-Wl,-rpath," + HERE], check=True)
     return out, exe
 
 

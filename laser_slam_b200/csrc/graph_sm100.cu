@@ -160,6 +160,7 @@ extern "C" zhsm_status zhsm_gate_candidates(zhsm_handle *h, const double *pose, 
     for (int m = 0; m < M; m++) if (cur_idx[m] < 0 || cur_idx[m] >= N) { h->err = "zhsm_gate_candidates: node index out of range"; return ZHSM_ERR_ARG; }
     if (M == 0) return ZHSM_OK;
     ZHSM_CUDA_TRY(h, cudaSetDevice(h->device));
+    StreamScope scope(h, h->stream);
     Dev d(h, h->stream);
     const double *dp = d.up(pose, 3 * (size_t)N), *dl = d.up(ld, 2 * (size_t)N), *dr = d.up(ru, 2 * (size_t)N);
     const double *dc = cov_xy ? d.up(cov_xy, 2 * (size_t)N) : nullptr;
@@ -180,6 +181,7 @@ extern "C" zhsm_status zhsm_available_area(zhsm_handle *h, const double *trans, 
     if (!trans || !ok || M < 0) { h->err = "zhsm_available_area: bad argument"; return ZHSM_ERR_ARG; }
     if (M == 0) return ZHSM_OK;
     ZHSM_CUDA_TRY(h, cudaSetDevice(h->device));
+    StreamScope scope(h, h->stream);
     Dev d(h, h->stream);
     const double *dt = d.up(trans, 3 * (size_t)M);
     const double *dc = cov_xy ? d.up(cov_xy, 2 * (size_t)M) : nullptr;
@@ -201,6 +203,7 @@ extern "C" zhsm_status zhsm_consensus(zhsm_handle *h, const double *poses, const
     for (int s = 0; s < S; s++) if (set_off[s + 1] < set_off[s] || set_off[0] != 0) { h->err = "zhsm_consensus: set offsets must start at 0 and not decrease"; return ZHSM_ERR_ARG; }
     const size_t total = (size_t)set_off[S];
     ZHSM_CUDA_TRY(h, cudaSetDevice(h->device));
+    StreamScope scope(h, h->stream);
     Dev d(h, h->stream);
     const double *dp = d.up(poses, 3 * total);
     const float *dg = d.up(good, total);

@@ -198,6 +198,15 @@ __global__ void __launch_bounds__(T, 3) icp_kernel(IcpArgs a) {
     const int job = blockIdx.x, t = threadIdx.x, lane = t & 31, w = t >> 5;
     const zhsm_icp_options &o = a.opt;
     const int rc = a.ref_idx[job], cc = a.cur_idx[job];
+    if ((unsigned)rc >= (unsigned)a.C || (unsigned)cc >= (unsigned)a.C) {
+        // device-resident job lists are not checked by the host: a bad index fails its own job, never the batch
+        if (t == 0) {
+            zhsm_result r = {};
+            r.status = ZHSM_JOB_INVALID_SCAN;
+            a.results[job] = r;
+        }
+        return;
+    }
     const int N1 = a.cnt[rc], N2 = a.cnt[cc];
     const float *g1 = a.pts + 2 * (size_t)a.off[rc], *g2 = a.pts + 2 * (size_t)a.off[cc];
     float gxmin = FLT_MAX, gxmax = -FLT_MAX, gymin = FLT_MAX, gymax = -FLT_MAX;

@@ -1,7 +1,5 @@
 // laser_slam_b200/csrc/plicp2_dispatch.cu -- host side of the PL-ICP kernel: CTA shape per beam count, the GF(2)
 // matrices of the parallel ld_corr_hash, and the launch dispatch over the compiled instances.
-#include <stdlib.h>
-
 #include <vector>
 
 #include "zhsm_internal.h"
@@ -17,15 +15,12 @@ cudaError_t plicp_launch_t512(const PlicpArgs &a, cudaStream_t st);
 //   n <= 640: 128 threads;  n <= 1472: 192 threads, 80 registers (4 CTAs/SM at 1080 beams, 3 up to 1472);
 //   n <= 2304: 256 threads, 128 registers, 2 CTAs/SM (2048 beams), the COOP instance whose long walks are finished
 //   warp-wide (plicp2_search.cuh);  else 512 threads (COOP as well).
-// ZHSM_PLICP_T overrides (tuning only).  Measured on one B200: 1080 beams, 20k pairs: 192 threads 16.8 ms, 256 (2
+// knob_T (ZHSM_PLICP_T, read once in zhsm_create) overrides (tuning only).  Measured on one B200: 1080 beams, 20k pairs: 192 threads 16.8 ms, 256 (2
 // CTAs/SM) 23.9; 1440 beams, 10k pairs: 192: 21.4 ms, 256: 22.1; 1536 beams: 192: 24.3, 256: 22.7; 2048 beams, first
 // guess 0, 4000 pairs: 256: 29.8 ms, 512 (1 CTA/SM): 36.6.
-void plicp_shape(int n, int *T, int *C, int *hash_chunk) {
+void plicp_shape(int n, int knob_T, int *T, int *C, int *hash_chunk) {
     int t = n <= 640 ? 128 : n <= 1472 ? 192 : n <= 2304 ? 256 : 512;
-    if (const char *e = getenv("ZHSM_PLICP_T")) {
-        int v = atoi(e);
-        if (v == 128 || v == 192 || v == 256 || v == 512) t = v;
-    }
+    if (knob_T == 128 || knob_T == 192 || knob_T == 256 || knob_T == 512) t = knob_T;
     while ((n + t - 1) / t > 32 && t < 512) t = t < 128 ? 128 : t < 256 ? 256 : 512;
     *T = t;
     *C = (n + t - 1) / t;
@@ -52,19 +47,19 @@ void plicp_build_hash_matrices(int n, int T, int ch, std::vector<uint32_t> &mat)
 }
 
 size_t plicp_jump_bytes_per_job(int n);
-cudaError_t plicp_jump_launch(const PlicpArgs &a, short *jt, cudaStream_t st);
+cudaError_t plicp_jump_launch(const PlicpArgs &a, short *jt, int32_t *owner, cudaStream_t st, int *launched);
 
-// a.jt must point at B * plicp_jump_bytes_per_job(n) bytes of scratch: the jump-table kernel fills it, the PL-ICP
-// kernel reads it (same stream).
+// a.jt must point at B * plicp_jump_bytes_per_job(n) bytes of scratch and a.owner at S ints: the owner / jump-table
+// kernels fill them, the PL-ICP kernel reads them (same stream).  a.T / a.hash_chunk are the shape the handle's hash
+// matrices were built for (zhsm_set_laser): the launch uses exactly that shape.
 cudaError_t plicp_launch(const PlicpArgs &a, int sm_count, cudaStream_t st, int *launched) {
     (void)sm_count;
-    int T, C, ch;
-    plicp_shape(a.L.n, &T, &C, &ch);
-    if (C > 32 || ch != a.hash_chunk) return cudaErrorInvalidValue;
-    if (!a.jt) return cudaErrorInvalidValue;
-    cudaError_t e = plicp_jump_launch(a, const_cast<short *>(a.jt), st);
+    const int T = a.T, C = (a.L.n + T - 1) / T;
+    if ((T != 128 && T != 192 && T != 256 && T != 512) || C > 32 || (a.hash_chunk & 1) || a.hash_chunk < C)
+        return cudaErrorInvalidValue;
+    if (!a.jt || !a.owner) return cudaErrorInvalidValue;
+    cudaError_t e = plicp_jump_launch(a, const_cast<short *>(a.jt), const_cast<int32_t *>(a.owner), st, launched);
     if (e != cudaSuccess) return e;
-    if (launched) *launched += 1;
     e = T == 128 ? plicp_launch_t128(a, st) : T == 192 ? plicp_launch_t192(a, st) : T == 256 ? plicp_launch_t256(a, st) : plicp_launch_t512(a, st);
     if (e == cudaSuccess && launched) *launched += 1;
     return e;

@@ -80,6 +80,22 @@ __device__ __forceinline__ int jt_search_down(const float *key, const float *m8,
 
 constexpr int JT_THREADS = 256;
 
+// Jobs that share a ref scan (the G starts of a multi-start pair, many-to-one loop-closure candidates) share its
+// tables: the lowest job of the launch that uses a scan OWNS it, builds the tables into its own scratch slot, and the
+// others read that slot.  owner[] is per scan; only the entries this launch touches are reset and claimed.
+__global__ void owner_reset_kernel(const int32_t *ref_idx, int B, int S, int32_t *owner) {
+    const int job = blockIdx.x * blockDim.x + threadIdx.x;
+    if (job >= B) return;
+    const int r = ref_idx[job];
+    if ((unsigned)r < (unsigned)S) owner[r] = 0x7fffffff;
+}
+__global__ void owner_claim_kernel(const int32_t *ref_idx, int B, int S, int32_t *owner) {
+    const int job = blockIdx.x * blockDim.x + threadIdx.x;
+    if (job >= B) return;
+    const int r = ref_idx[job];
+    if ((unsigned)r < (unsigned)S) atomicMin(&owner[r], job);
+}
+
 // jt: [B][2][n][2] shorts: per job the pairs (up_bigger, up_smaller)[n] then (down_bigger, down_smaller)[n] of its
 // ref scan -- the walk fetches both jumps of a direction with one 32-bit load
 __global__ void __launch_bounds__(JT_THREADS) jump_tables_kernel(PlicpArgs a, short *jt) {
@@ -92,7 +108,9 @@ __global__ void __launch_bounds__(JT_THREADS) jump_tables_kernel(PlicpArgs a, sh
     float *hi64 = lo8 + nb8, *lo64 = hi64 + nb64;
     float *any8 = lo64 + nb64, *any64 = any8 + nb8;  // max(key): >= 0 when the block holds a valid ray
     const int job = blockIdx.x;
-    const float *row = a.scans + (size_t)a.ref_idx[job] * n;
+    const int ref = a.ref_idx[job];
+    if ((unsigned)ref >= (unsigned)a.S || a.owner[ref] != job) return;  // bad index (the PL-ICP kernel reports it) / not the owner
+    const float *row = a.scans + (size_t)ref * n;
     const int rounds = (n + JT_THREADS - 1) / JT_THREADS;
     for (int k = 0; k < rounds; k++) {
         const int i = k * JT_THREADS + t;
@@ -146,8 +164,11 @@ __global__ void __launch_bounds__(JT_THREADS) jump_tables_kernel(PlicpArgs a, sh
 
 size_t plicp_jump_bytes_per_job(int n) { return sizeof(short) * 4 * (size_t)n; }
 
-cudaError_t plicp_jump_launch(const PlicpArgs &a, short *jt, cudaStream_t st) {
+cudaError_t plicp_jump_launch(const PlicpArgs &a, short *jt, int32_t *owner, cudaStream_t st, int *launched) {
     const int n = a.L.n;
+    plicp2::owner_reset_kernel<<<(a.B + 255) / 256, 256, 0, st>>>(a.ref_idx, a.B, a.S, owner);
+    plicp2::owner_claim_kernel<<<(a.B + 255) / 256, 256, 0, st>>>(a.ref_idx, a.B, a.S, owner);
+    if (launched) *launched += 3;
     const int nb8 = (n + 7) >> 3, nb64 = (nb8 + 7) >> 3;
     const size_t smem = sizeof(float) * (size_t)(((n + 31) & ~31) + 3 * nb8 + 3 * nb64);
     if (smem > 48 * 1024) {

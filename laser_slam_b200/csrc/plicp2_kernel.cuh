@@ -289,12 +289,24 @@ __global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 2 : 1)) plicp2_k
     PhaseClock pc;
     pc.start();
     // ---------------- load + fromPMScan2LDP + ld_valid_fields + ld_invalid_if_outside + ld_compute_cartesian
-    const float *ref_row = a.scans + (size_t)a.ref_idx[job] * n;
-    const float *sens_row = a.scans + (size_t)a.sens_idx[job] * n;
+    const int ref_i = a.ref_idx[job], sens_i = a.sens_idx[job];
+    if ((unsigned)ref_i >= (unsigned)a.S || (unsigned)sens_i >= (unsigned)a.S) {
+        // device-resident job lists are not checked by the host: a bad index fails its own job, never the batch
+        if (t == 0) {
+            zhsm_result r = {};
+            r.status = ZHSM_JOB_INVALID_SCAN;
+            a.results[job] = r;
+        }
+        if (a.corr_j1) for (int i = t; i < n; i += T) { a.corr_j1[(size_t)job * n + i] = -1; a.corr_j2[(size_t)job * n + i] = -1; }
+        return;
+    }
+    const float *ref_row = a.scans + (size_t)ref_i * n;
+    const float *sens_row = a.scans + (size_t)sens_i * n;
     int bad_field = 0, nvf_ref = 0, nvf_sens = 0;
     unsigned sens = 0;
-    // jump tables of this job's ref scan, built by jump_tables_kernel (plicp2_jump.cu): 8 bytes per ray
-    const uint2 *jt_job = reinterpret_cast<const uint2 *>(a.jt + (size_t)job * 4 * n);
+    // jump tables of this job's ref scan, built by jump_tables_kernel (plicp2_jump.cu) in the slot of the scan's owning
+    // job: 8 bytes per ray
+    const uint2 *jt_job = reinterpret_cast<const uint2 *>(a.jt + (size_t)a.owner[ref_i] * 4 * n);
     if (!l.jt_shared) {
         uint2 *dst = PL_SH(uint2, l.jt);
         for (int q = t; q < n; q += T) dst[q] = __ldcs(jt_job + q);

@@ -26,6 +26,15 @@ __global__ void __launch_bounds__(T) psm_kernel(Args a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const Sh s = carve(smem_raw, a.L.n);
     const int job = blockIdx.x;
+    if ((unsigned)a.act_idx[job] >= (unsigned)a.S || (unsigned)a.ref_idx[job] >= (unsigned)a.S) {
+        // device-resident job lists are not checked by the host: a bad index fails its own job, never the batch
+        if (threadIdx.x == 0) {
+            zhsm_result r = {};
+            r.status = ZHSM_JOB_INVALID_SCAN;
+            a.results[job] = r;
+        }
+        return;
+    }
     load_job(s, a, job, true);
     float pose[3] = {0, 0, 0};
     if (a.init_pose) for (int k = 0; k < 3; k++) pose[k] = a.init_pose[3 * (size_t)job + k];

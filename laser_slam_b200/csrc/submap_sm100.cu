@@ -157,6 +157,7 @@ extern "C" zhsm_status zhsm_submap_cloud(zhsm_handle *h, const float *scans, con
     if (!h->have_laser) { h->err = "zhsm_set_laser not called"; return ZHSM_ERR_ARG; }
     ZHSM_CUDA_TRY(h, cudaSetDevice(h->device));
     cudaStream_t st = h->stream;
+    StreamScope scope(h, st);
     const int n = h->laser.n;
     const size_t tot = (size_t)K * n;
     void *p;

@@ -127,6 +127,7 @@ extern "C" zhsm_status zhsm_synth_pairs(zhsm_handle *h, float *d_scans, double *
     if (npairs == 0) return ZHSM_OK;
     ZHSM_CUDA_TRY(h, cudaSetDevice(h->device));
     cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : h->stream;
+    StreamScope scope(h, st);
     synth_pairs_kernel<<<npairs, 128, 0, st>>>(d_scans, d_truth, first_pair, npairs, h->laser.n, h->laser.fi_min,
                                                h->laser.dfi, h->laser.max_range_cm, dmax_xy_m, dmax_th_rad, noise_m,
                                                dropout, seed);

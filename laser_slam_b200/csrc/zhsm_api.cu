@@ -106,10 +106,16 @@ extern "C" zhsm_status zhsm_create(int device, zhsm_handle **out) {
     h->device = device;
     h->sm_count = prop.multiProcessorCount;
     if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaEventCreate(&h->ev0) != cudaSuccess || cudaEventCreate(&h->ev1) != cudaSuccess) {
-        delete h;
+        cudaEventCreate(&h->ev0) != cudaSuccess || cudaEventCreate(&h->ev1) != cudaSuccess ||
+        cudaEventCreateWithFlags(&h->ev_busy, cudaEventDisableTiming) != cudaSuccess) {
+        zhsm_destroy(h);
         return ZHSM_ERR_CUDA;
     }
+    // tuning knobs: read here once, clamped; the launch path never looks at the environment
+    if (const char *e = getenv("ZHSM_PLICP_T")) { int v = atoi(e); if (v == 128 || v == 192 || v == 256 || v == 512) h->knob_T = v; }
+    if (const char *e = getenv("ZHSM_PLICP_CHUNK")) { int v = atoi(e); if (v >= 1 && v <= (1 << 22)) h->knob_chunk = v; }
+    if (const char *e = getenv("ZHSM_PLICP_CHUNK_ITERS")) { int v = atoi(e); if (v >= 0 && v <= ZHSM_MAX_ITER) h->knob_chunk_iters = v; }
+    if (const char *e = getenv("ZHSM_PLICP_SMEM_PAD")) { int v = atoi(e); if (v >= 0 && v <= 160 * 1024) h->knob_smem_pad = v & ~15; }
     *out = h;
     return ZHSM_OK;
 }
@@ -118,7 +124,7 @@ extern "C" void zhsm_destroy(zhsm_handle *h) {
     if (!h) return;
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
-    for (int i = 0; i < 16; i++) if (h->d_stage[i]) cudaFree(h->d_stage[i]);
+    for (int i = 0; i < ZHSM_STAGE_SLOTS; i++) if (h->d_stage[i]) cudaFree(h->d_stage[i]);
     if (h->d_fi) cudaFree(h->d_fi);
     if (h->d_si) cudaFree(h->d_si);
     if (h->d_co) cudaFree(h->d_co);
@@ -126,6 +132,7 @@ extern "C" void zhsm_destroy(zhsm_handle *h) {
     if (h->d_hashmat) cudaFree(h->d_hashmat);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
+    if (h->ev_busy) cudaEventDestroy(h->ev_busy);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -151,7 +158,11 @@ extern "C" zhsm_status zhsm_sync(zhsm_handle *h, void *cuda_stream) {
 extern "C" zhsm_status zhsm_set_laser(zhsm_handle *h, const zhsm_laser *laser) {
     if (!h || !laser) return ZHSM_ERR_ARG;
     if (laser->n < 10 || laser->n > ZHSM_MAX_BEAMS) { h->err = "laser.n out of range [10,4096]"; return ZHSM_ERR_ARG; }
+    if (h->have_laser && memcmp(&h->laser, laser, sizeof(*laser)) == 0) return ZHSM_OK;  // tables already built
     ZHSM_CUDA_TRY(h, cudaSetDevice(h->device));
+    // the tables are replaced: wait for everything that may still read the old ones (any stream this handle was used on)
+    if (h->busy_valid) ZHSM_CUDA_TRY(h, cudaEventSynchronize(h->ev_busy));
+    h->have_laser = false;
     const int n = laser->n;
     std::vector<double2> cs(n);
     for (int i = 0; i < n; i++) {
@@ -183,7 +194,7 @@ extern "C" zhsm_status zhsm_set_laser(zhsm_handle *h, const zhsm_laser *laser) {
     // GF(2) matrices of the parallel ld_corr_hash for this beam count / CTA shape
     {
         int T, C, ch;
-        plicp_shape(n, &T, &C, &ch);
+        plicp_shape(n, h->knob_T, &T, &C, &ch);
         if (C > 32) { h->err = "no PL-ICP kernel instance for this beam count"; return ZHSM_ERR_UNSUPPORTED; }
         std::vector<uint32_t> mat;
         plicp_build_hash_matrices(n, T, ch, mat);
@@ -191,6 +202,8 @@ extern "C" zhsm_status zhsm_set_laser(zhsm_handle *h, const zhsm_laser *laser) {
         ZHSM_CUDA_TRY(h, cudaMalloc(&h->d_hashmat, sizeof(uint32_t) * mat.size()));
         ZHSM_CUDA_TRY(h, cudaMemcpy(h->d_hashmat, mat.data(), sizeof(uint32_t) * mat.size(), cudaMemcpyHostToDevice));
         h->hash_chunk = ch;
+        h->hash_T = T;  // the launch uses exactly the shape these matrices were built for
+        h->hash_C = C;
     }
     h->laser = *laser;
     h->have_laser = true;
@@ -202,7 +215,7 @@ extern "C" zhsm_status zhsm_set_laser(zhsm_handle *h, const zhsm_laser *laser) {
 extern "C" int zhsm_debug_corr_hash(const int32_t *stream, int n, uint32_t *seq, uint32_t *par) {
     if (!stream || n < 1 || n > ZHSM_MAX_BEAMS || !seq || !par) return 1;
     int T, C, ch;
-    plicp_shape(n, &T, &C, &ch);
+    plicp_shape(n, 0, &T, &C, &ch);
     if (C > 32) return 2;
     std::vector<uint32_t> mat;
     plicp_build_hash_matrices(n, T, ch, mat);
@@ -260,6 +273,7 @@ extern "C" zhsm_status zhsm_median_filter_batch(zhsm_handle *h, float *scans, in
     if (S == 0) return ZHSM_OK;
     ZHSM_CUDA_TRY(h, cudaSetDevice(h->device));
     cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : h->stream;
+    StreamScope scope(h, st);
     const int n = h->laser.n;
     float *d = scans;
     size_t bytes = sizeof(float) * (size_t)S * n;
@@ -302,11 +316,15 @@ extern "C" zhsm_status zhsm_plicp_batch(zhsm_handle *h, const float *scans, int 
     if (P.max_iterations < 1 || P.max_iterations > ZHSM_MAX_ITER) { h->err = "max_iterations out of [1,64]"; return ZHSM_ERR_ARG; }
     ZHSM_CUDA_TRY(h, cudaSetDevice(h->device));
     cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : h->stream;
+    StreamScope scope(h, st);
     const int n = h->laser.n;
 
     PlicpArgs a;
     memset(&a, 0, sizeof(a));
     a.B = B;
+    a.S = S;
+    a.T = h->hash_T;
+    a.smem_pad = h->knob_smem_pad;
     a.P = P;
     a.L.n = n; a.L.fi_min = h->laser.fi_min; a.L.dfi = h->laser.dfi;
     a.L.min_range_cm = h->laser.min_range_cm; a.L.max_range_cm = h->laser.max_range_cm;
@@ -314,8 +332,7 @@ extern "C" zhsm_status zhsm_plicp_batch(zhsm_handle *h, const float *scans, int 
     a.cs = h->d_cs;
     a.hashmat = h->d_hashmat;
     a.hash_chunk = h->hash_chunk;
-    a.chunk_iters = 2;
-    if (const char *e = getenv("ZHSM_PLICP_CHUNK_ITERS")) a.chunk_iters = atoi(e);  // tuning only
+    a.chunk_iters = h->knob_chunk_iters;
 
     // ld_valid_fields' per-scan-geometry checks (laser_data.c): nrays, fov, theta[] consistent by construction
     {
@@ -373,11 +390,13 @@ extern "C" zhsm_status zhsm_plicp_batch(zhsm_handle *h, const float *scans, int 
     }
     // Jump tables of the jobs' ref scans go through a scratch buffer (8 bytes per ray and job); large batches are
     // cut into chunks so that the scratch stays bounded (ZHSM_PLICP_CHUNK jobs, default 131072 = 1.1 GB at 1080 beams).
-    int chunk = 131072;
-    if (const char *e = getenv("ZHSM_PLICP_CHUNK")) { int v = atoi(e); if (v >= 1) chunk = v; }
+    int chunk = h->knob_chunk;
     if (chunk > B) chunk = B;
     if ((s = zhsm_stage(h, 15, plicp_jump_bytes_per_job(n) * (size_t)chunk, &p)) != ZHSM_OK) return s;
     a.jt = (const short *)p;
+    // per scan: the job of the running launch that owns (builds) its jump tables -- jobs sharing a ref scan share them
+    if ((s = zhsm_stage(h, 16, sizeof(int32_t) * (size_t)S, &p)) != ZHSM_OK) return s;
+    a.owner = (const int32_t *)p;
     ZHSM_CUDA_TRY(h, cudaEventRecord(h->ev0, st));
     int launched = 0;
     for (int off = 0; off < B; off += chunk) {

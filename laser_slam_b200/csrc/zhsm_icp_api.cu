@@ -48,9 +48,11 @@ extern "C" zhsm_status zhsm_icp_batch(zhsm_handle *h, const float *pts, long lon
     }
     a.cap = cap;
     a.B = B;
+    a.C = C;
     if (icp_smem_bytes(cap) > 227 * 1024) { h->err = "zhsm_icp_batch: cloud too large for shared memory"; return ZHSM_ERR_UNSUPPORTED; }
     ZHSM_CUDA_TRY(h, cudaSetDevice(h->device));
     cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : h->stream;
+    StreamScope scope(h, st);
     zhsm_status s;
     void *p;
     if (flags & ZHSM_SCANS_ON_DEVICE) a.pts = pts;
@@ -108,6 +110,7 @@ extern "C" zhsm_status zhsm_best_of_starts(zhsm_handle *h, const zhsm_result *re
     if (P == 0) return ZHSM_OK;
     ZHSM_CUDA_TRY(h, cudaSetDevice(h->device));
     cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : h->stream;
+    StreamScope scope(h, st);
     if (flags & ZHSM_RESULTS_ON_DEVICE) {
         ZHSM_CUDA_TRY(h, best_of_starts_launch(results, P, G, criterion, best, best_results, st));
         h->launches++;

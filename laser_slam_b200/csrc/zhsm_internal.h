@@ -10,6 +10,7 @@
 
 #define ZHSM_MAX_BEAMS 4096
 #define ZHSM_MAX_ITER 64
+#define ZHSM_STAGE_SLOTS 24
 
 struct zhsm_handle {
     int device = 0;
@@ -19,6 +20,16 @@ struct zhsm_handle {
     uint64_t launches = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool ev_valid = false;
+    // The staging slots and scratch buffers belong to the handle, not to a call: every entry point orders its stream
+    // behind the last call that used them (StreamScope below), so calls on different streams never overlap on them.
+    cudaEvent_t ev_busy = nullptr;
+    bool busy_valid = false;
+    // tuning knobs, read from the environment ONCE in zhsm_create (never on the launch path) and clamped
+    int knob_T = 0;            // ZHSM_PLICP_T: 0 = by beam count, else 128 / 192 / 256 / 512
+    int knob_chunk = 131072;   // ZHSM_PLICP_CHUNK: jobs per launch (bounds the jump-table scratch)
+    int knob_chunk_iters = 2;  // ZHSM_PLICP_CHUNK_ITERS: first iterations searched in chunk order
+    int knob_smem_pad = 0;     // ZHSM_PLICP_SMEM_PAD: extra dynamic shared memory (fewer CTAs per SM)
+    int hash_T = 0, hash_C = 0;  // CTA shape the hash matrices were built for (zhsm_set_laser)
 
     bool have_laser = false;
     zhsm_laser laser{};
@@ -29,8 +40,22 @@ struct zhsm_handle {
     float *d_fi = nullptr, *d_si = nullptr, *d_co = nullptr;  // pm_fi / pm_si / pm_co (pm_init), host libm, float
 
     // staging for host-pointer calls
-    void *d_stage[16] = {nullptr};
-    size_t stage_bytes[16] = {0};
+    void *d_stage[ZHSM_STAGE_SLOTS] = {nullptr};
+    size_t stage_bytes[ZHSM_STAGE_SLOTS] = {0};
+};
+
+// Orders `st` behind the handle's previous call (any stream) on entry and marks the handle busy until everything this
+// call queued on `st` is done.  One per entry point that touches staging / scratch buffers.
+struct StreamScope {
+    zhsm_handle *h;
+    cudaStream_t st;
+    StreamScope(zhsm_handle *h_, cudaStream_t st_) : h(h_), st(st_) {
+        if (h->busy_valid) cudaStreamWaitEvent(st, h->ev_busy, 0);
+    }
+    ~StreamScope() {
+        if (cudaEventRecord(h->ev_busy, st) == cudaSuccess) h->busy_valid = true;
+        else cudaGetLastError();
+    }
 };
 
 // device-side geometry passed by value to kernels
@@ -49,7 +74,12 @@ struct PlicpArgs {
     zhsm_result *results;    // [B]
     int16_t *corr_j1, *corr_j2; // [B][n] or null
     const double2 *cs;       // [n]
-    const short *jt;         // [B][2][n][2] jump tables of each job's ref scan (plicp2_jump.cu)
+    const short *jt;         // [B][2][n][2] jump tables (plicp2_jump.cu): slot k holds the tables of job k's ref scan
+                             // when job k is the OWNER of that scan (lowest job of the launch that uses it)
+    const int32_t *owner;    // [S] per scan: the owning job of this launch (jobs sharing a ref scan share its tables)
+    int S;                   // scans in the pool (device-side range check of the job indices)
+    int T;                   // CTA shape the handle's hash matrices were built for
+    int smem_pad;            // tuning: extra dynamic shared memory per CTA
     const uint32_t *hashmat; // [T][32] GF(2) matrices of the parallel ld_corr_hash (plicp2_select.cuh)
     int hash_chunk;          // stream elements hashed per thread (even)
     int chunk_iters;         // first iterations of an icp_loop searched in chunk order (find_correspondences)
@@ -69,6 +99,7 @@ struct PsmArgs {
     unsigned char *proj_bad;     // scan_project mode: [B][n]
     const float *fi, *si, *co;   // [n] host-libm tables (pm_init, ZHPolar_Match.cpp:68-78)
     int B, algo;
+    int S;                       // scans in the pool (device-side range check of the job indices)
     LaserDev L;
 };
 cudaError_t psm_launch(const PsmArgs &a, int mode, cudaStream_t st);  // mode 0 matcher, 1 scan_project
@@ -80,6 +111,7 @@ struct IcpArgs {
     const int32_t *ref_idx, *cur_idx;  // [B]
     const double *init;          // [B][3] or null
     zhsm_result *results;        // [B]
+    int C;                       // clouds in the pool (device-side range check of the job indices)
     int B, cap;                  // cap = capacity (points) of the shared-memory arrays = largest cloud
     zhsm_icp_options opt;
 };
@@ -94,7 +126,7 @@ zhsm_status zhsm_stage(zhsm_handle *h, int slot, size_t bytes, void **out);
 cudaError_t plicp_launch(const PlicpArgs &a, int sm_count, cudaStream_t st, int *launched);
 size_t plicp_jump_bytes_per_job(int n);
 // CTA shape the PL-ICP kernel uses for n beams: T threads, C rays per thread, hash chunk (even) per thread
-void plicp_shape(int n, int *T, int *C, int *hash_chunk);
+void plicp_shape(int n, int knob_T, int *T, int *C, int *hash_chunk);
 void plicp_build_hash_matrices(int n, int T, int ch, std::vector<uint32_t> &mat);
 cudaError_t median_filter_launch(float *scans, int S, int n, cudaStream_t st);
 

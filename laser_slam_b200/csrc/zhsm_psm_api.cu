@@ -38,6 +38,7 @@ extern "C" zhsm_status zhsm_preprocess_batch(zhsm_handle *h, float *scans, uint8
     if (S == 0) return ZHSM_OK;
     ZHSM_CUDA_TRY(h, cudaSetDevice(h->device));
     cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : h->stream;
+    StreamScope scope(h, st);
     const size_t n = h->laser.n, cnt = (size_t)S * n;
     float *ds = scans;
     uint8_t *db = bad;
@@ -80,9 +81,10 @@ extern "C" zhsm_status zhsm_psm_batch(zhsm_handle *h, const float *scans, const 
     if (B == 0) return ZHSM_OK;
     ZHSM_CUDA_TRY(h, cudaSetDevice(h->device));
     cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : h->stream;
+    StreamScope scope(h, st);
     PsmArgs a;
     memset(&a, 0, sizeof(a));
-    a.B = B; a.algo = algo; a.L = laser_dev(h);
+    a.B = B; a.algo = algo; a.S = S; a.L = laser_dev(h);
     a.fi = h->d_fi; a.si = h->d_si; a.co = h->d_co;
     zhsm_status s;
     if ((s = stage_scans(h, scans, bad, seg, S, flags, st, &a.scans, &a.bad, (const int16_t **)&a.seg)) != ZHSM_OK) return s;
@@ -126,10 +128,13 @@ extern "C" zhsm_status zhsm_scan_project_batch(zhsm_handle *h, const float *scan
     if (!h->have_laser) { h->err = "zhsm_set_laser not called"; return ZHSM_ERR_ARG; }
     ZHSM_CUDA_TRY(h, cudaSetDevice(h->device));
     cudaStream_t st = h->stream;
+    StreamScope scope(h, st);
     const size_t n = h->laser.n;
+    for (int k = 0; k < B; k++)
+        if (idx[k] < 0 || idx[k] >= S) { h->err = "zhsm_scan_project_batch: scan index out of range"; return ZHSM_ERR_ARG; }
     PsmArgs a;
     memset(&a, 0, sizeof(a));
-    a.B = B; a.L = laser_dev(h);
+    a.B = B; a.S = S; a.L = laser_dev(h);
     a.fi = h->d_fi; a.si = h->d_si; a.co = h->d_co;
     zhsm_status s;
     if ((s = stage_scans(h, scans, bad, seg, S, 0, st, &a.scans, &a.bad, (const int16_t **)&a.seg)) != ZHSM_OK) return s;
@@ -159,6 +164,7 @@ extern "C" zhsm_status zhsm_is_corridor_batch(zhsm_handle *h, const float *scans
     if (S == 0) return ZHSM_OK;
     ZHSM_CUDA_TRY(h, cudaSetDevice(h->device));
     cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : h->stream;
+    StreamScope scope(h, st);
     const float *ds; const uint8_t *db; const int16_t *dg;
     zhsm_status s;
     if ((s = stage_scans(h, scans, bad, seg, S, flags, st, &ds, &db, &dg)) != ZHSM_OK) return s;

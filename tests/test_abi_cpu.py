@@ -23,9 +23,13 @@ def lib():
 
 
 def _declared_symbols():
-    txt = open(os.path.join(ROOT, "include", "zhsm.h")).read()
-    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
-    return sorted(set(re.findall(r"\b(zhsm_[a-z0-9_]+)\s*\(", txt)))
+    syms = set()
+    for hdr in ("zhsm.h", "csm_compat.h"):
+        txt = open(os.path.join(ROOT, "include", hdr)).read()
+        txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+        txt = re.sub(r"static inline[^{]*\{[^}]*\}", "", txt)
+        syms |= set(re.findall(r"\b(zhsm_[a-z0-9_]+|sm_icp|sm_debug_write|ld_alloc_new|ld_free)\s*\(", txt))
+    return sorted(syms)
 
 
 def test_header_symbols_exported(lib):
@@ -119,3 +123,80 @@ def test_corr_hash_chunk_algebra(lib):
                     h ^= (~(((h << 11) & 0xFFFFFFFF) ^ x ^ (h >> 5))) & 0xFFFFFFFF
             assert seq.value == (h & 0x7FFFFFFF)
             assert par.value == seq.value, n
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# the CSM-shaped entry (include/csm_compat.h): what can be checked without a GPU
+# ---------------------------------------------------------------------------------------------------------------
+CSM_PROBE = r"""
+#include <csm/csm_all.h>
+#include <csm/algos.h>
+#include <csm/logging.h>
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+static void fill(LDP ld, float fi_min, float dfi, double reading) {
+    int i;
+    for (i = 0; i < ld->nrays; i++) {
+        ld->valid[i] = 1; ld->readings[i] = reading; ld->theta[i] = fi_min + dfi * (unsigned)i; ld->cluster[i] = -1;
+    }
+    ld->min_theta = ld->theta[0]; ld->max_theta = ld->theta[ld->nrays - 1];
+}
+int main(void) {
+    struct sm_params in; struct sm_result out;
+    LDP a = ld_alloc_new(181), b = ld_alloc_new(181);
+    int i, bad = 0;
+    if (!a || !b || a->nrays != 181) return 1;
+    for (i = 0; i < 181; i++) bad |= a->valid[i] != 0 || a->cluster[i] != -1 || a->corr[i].valid != 0 || a->corr[i].j1 != -1 || !isnan(a->readings[i]);
+    if (bad) return 2;
+    memset(&in, 0, sizeof(in));
+    in.laser_ref = a; in.laser_sens = b; in.use_corr_tricks = 1; in.use_point_to_line_distance = 1; in.max_iterations = 10;
+    in.min_reading = 0.1; in.max_reading = 50;
+    sm_debug_write(0);
+    /* 1: unfilled scans (NaN theta) are rejected like ld_valid_fields rejects them */
+    sm_icp(&in, &out);
+    if (out.valid != 0 || out.status != -1) return 3;
+    /* 2: a theta[] that is not a float progression is refused, loudly */
+    fill(a, -1.5707964f, 0.017453292f, (double)123.5f / 100.0); fill(b, -1.5707964f, 0.017453292f, (double)123.5f / 100.0);
+    a->theta[7] += 1e-9; b->theta[7] += 1e-9;
+    sm_icp(&in, &out);
+    if (out.valid != 0 || out.status != -1) return 4;
+    /* 3: readings that are not float-centimetre values are refused */
+    fill(a, -1.5707964f, 0.017453292f, 1.2345678901234); fill(b, -1.5707964f, 0.017453292f, 1.2345678901234);
+    sm_icp(&in, &out);
+    if (out.valid != 0 || out.status != -1) return 5;
+    /* 4: unsupported settings are refused */
+    fill(a, -1.5707964f, 0.017453292f, (double)123.5f / 100.0); fill(b, -1.5707964f, 0.017453292f, (double)123.5f / 100.0);
+    in.use_corr_tricks = 0;
+    sm_icp(&in, &out);
+    if (out.valid != 0 || out.status != -1) return 6;
+    in.use_corr_tricks = 1;
+    /* 5: a well-formed call reaches the engine: valid only with a GPU; without one valid = 0 (no CPU matcher) */
+    sm_icp(&in, &out);
+    printf("engine_valid=%d status=%d\n", out.valid, out.status);
+    ld_free(a); ld_free(b);
+    { gsl_matrix *m = zhsm_gsl_matrix_alloc(3, 3); gsl_matrix_set(m, 1, 2, 4.5); if (gsl_matrix_get(m, 1, 2) != 4.5 || gsl_matrix_get(m, 2, 1) != 0) return 7; zhsm_gsl_matrix_free(m); }
+    return 0;
+}
+"""
+
+
+def test_csm_entry_plain_c_links_against_libzhsm_only(lib, tmp_path):
+    """include/csm/*.h forward to csm_compat.h; a plain-C program using sm_icp / ld_alloc_new / ld_free /
+    gsl_matrix_get links against libzhsm.so alone; malformed inputs are refused with valid = 0 (never a different
+    algorithm); without a GPU a well-formed call reports valid = 0 (there is no CPU matcher)."""
+    src = tmp_path / "probe.c"
+    src.write_text(CSM_PROBE)
+    exe = tmp_path / "probe"
+    libdir = os.path.dirname(zh.lib_path())
+    p = subprocess.run(["gcc", "-std=gnu99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe),
+                        "-L" + libdir, "-lzhsm", "-lm", "-Wl,-rpath," + libdir], capture_output=True)
+    assert p.returncode == 0, p.stderr.decode()
+    r = subprocess.run([str(exe)], capture_output=True)
+    assert r.returncode == 0, (r.returncode, r.stderr.decode())
+    import torch
+    if not torch.cuda.is_available():
+        assert b"engine_valid=0 status=-1" in r.stdout
+        assert b"no usable sm_100 GPU" in r.stderr
+    needed = subprocess.run(["readelf", "-d", str(exe)], capture_output=True).stdout.decode()
+    assert "libzhsm.so" in needed and "csm" not in needed.replace("libzhsm", "").lower()

@@ -226,3 +226,62 @@ def test_plicp_long_scans_poor_guesses_match_oracle():
     o = po.zhcsm_fmatch_batch(scans, ri, si, lz.fi_min, lz.dfi, 10, 3000, first_guess=guess, nthreads=8)
     _assert_same_as_oracle(res, o, min_frac=0.995)
     assert (res["valid"] == 1).mean() > 0.9
+
+
+def test_overlapping_batches_on_two_streams_of_one_handle():
+    """The staging slots and the jump-table scratch belong to the handle: two batches issued back to back on two
+    different streams (results left on the device, so neither call blocks) must give the records of the serial run --
+    every entry orders its stream behind the handle's previous call (StreamScope, zhsm_internal.h)."""
+    import torch
+    import laser_slam_b200 as zh
+    g = load_log("intel-lab")
+    eng = zh.Engine(0)
+    eng.set_laser(make_laser(g))
+    dev = torch.device("cuda:0")
+    host = eng.median_filter(g["scans"][:1201].copy())
+    a_h, b_h = host[:601], host[600:1201]
+    idx = np.arange(600, dtype=np.int32)
+    want_a = eng.plicp(a_h, idx, idx + 1)
+    want_b = eng.plicp(b_h, idx, idx + 1)
+    s1, s2 = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+    for rep in range(3):
+        ra = torch.zeros((600, 128), dtype=torch.uint8, device=dev)
+        rb = torch.zeros((600, 128), dtype=torch.uint8, device=dev)
+        # host scans + host job lists -> staged by the handle; device results -> the calls return while kernels run
+        eng.plicp(a_h, idx, idx + 1, results=ra, stream=s1.cuda_stream)
+        eng.plicp(b_h, idx, idx + 1, results=rb, stream=s2.cuda_stream)
+        torch.cuda.synchronize()
+        got_a = ra.cpu().numpy().view(zh.RESULT_DTYPE).reshape(-1)
+        got_b = rb.cpu().numpy().view(zh.RESULT_DTYPE).reshape(-1)
+        for got, want in ((got_a, want_a), (got_b, want_b)):
+            assert np.array_equal(got["corr_hash"], want["corr_hash"]) and np.array_equal(got["iterations"], want["iterations"])
+            assert np.array_equal(got["x"], want["x"])
+    eng.close()
+
+
+def test_bad_device_job_index_fails_its_own_job_only():
+    """Device-resident job lists are not checked by the host: an out-of-range scan index must fail that job with
+    ZHSM_JOB_INVALID_SCAN and leave the rest of the batch intact."""
+    import torch
+    import laser_slam_b200 as zh
+    g = load_log("fr079")
+    eng = zh.Engine(0)
+    eng.set_laser(make_laser(g))
+    dev = torch.device("cuda:0")
+    scans = torch.from_numpy(eng.median_filter(g["scans"][:65].copy())).to(dev)
+    ri = torch.arange(0, 64, dtype=torch.int32, device=dev)
+    si = ri + 1
+    good = torch.zeros((64, 128), dtype=torch.uint8, device=dev)
+    eng.plicp(scans, ri, si, results=good)
+    ri2, si2 = ri.clone(), si.clone()
+    ri2[5] = 65; si2[9] = -3; ri2[40] = 1 << 30
+    out = torch.zeros((64, 128), dtype=torch.uint8, device=dev)
+    eng.plicp(scans, ri2, si2, results=out)
+    eng.sync()
+    a = good.cpu().numpy().view(zh.RESULT_DTYPE).reshape(-1)
+    b = out.cpu().numpy().view(zh.RESULT_DTYPE).reshape(-1)
+    badj = np.array([5, 9, 40])
+    assert (b["valid"][badj] == 0).all() and (b["status"][badj] == 4).all()
+    rest = np.setdiff1d(np.arange(64), badj)
+    assert np.array_equal(a[rest].tobytes(), b[rest].tobytes())
+    eng.close()
