@@ -50,8 +50,12 @@ typedef struct zhsm_laser {
     int32_t max_range_cm;     /* pm_max_range */
     int32_t min_valid_points; /* pm_min_valid_points */
     int32_t scan_window;      /* pm_scan_window */
-    int32_t reserved;
+    int32_t flags;            /* ZHSM_LASER_* */
 } zhsm_laser;
+/* pm_orientation_search's branch for pm_laser_name == "HOKUYO_UTM_30LX" (ZHPolar_Match.cpp:1182-1191): a beam only
+ * counts towards a shift's error when |new_r - ref_r| < PM_MAX_ERROR (100 cm).  The reference keys it on the sensor's
+ * name; here it is a flag of the geometry so that any Hokuyo-class laser can ask for it. */
+#define ZHSM_LASER_UTM_GATE 1
 
 /* The sm_params fields CCanonicalMatcher::sm_init sets (src/zhcsm/ZHCanonical_Matcher.cpp:83-157).
  * zhsm_plicp_default_params() fills the reference's values. */

@@ -20,9 +20,17 @@ __device__ __forceinline__ float orientation_search(const Sh &s, const LaserDev 
         int min_i, max_i;
         if (di <= 0) { min_i = -di; max_i = n; } else { min_i = 0; max_i = n - di; }
         float e = 0, cnt = 0;
-        for (int i = min_i; i < max_i; i++) {
-            const float delta = fabsf(s.new_r[i] - s.ref_r[i + di]);
-            if (!s.new_bad[i] && !s.ref_bad[i + di]) { e += delta; cnt++; }
+        if (L.flags & ZHSM_LASER_UTM_GATE) {
+            // the "HOKUYO_UTM_30LX" branch (:1182-1191): delta < PM_MAX_ERROR (100 cm) picks the right local minimum
+            for (int i = min_i; i < max_i; i++) {
+                const float delta = fabsf(s.new_r[i] - s.ref_r[i + di]);
+                if (!s.new_bad[i] && !s.ref_bad[i + di] && delta < 100.f) { e += delta; cnt++; }
+            }
+        } else {
+            for (int i = min_i; i < max_i; i++) {
+                const float delta = fabsf(s.new_r[i] - s.ref_r[i + di]);
+                if (!s.new_bad[i] && !s.ref_bad[i + di]) { e += delta; cnt++; }
+            }
         }
         s.err[k] = cnt > 0 ? e / cnt : LARGE_NUMBER;
     }

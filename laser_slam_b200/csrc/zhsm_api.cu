@@ -329,6 +329,7 @@ extern "C" zhsm_status zhsm_plicp_batch(zhsm_handle *h, const float *scans, int 
     a.L.n = n; a.L.fi_min = h->laser.fi_min; a.L.dfi = h->laser.dfi;
     a.L.min_range_cm = h->laser.min_range_cm; a.L.max_range_cm = h->laser.max_range_cm;
     a.L.min_valid_points = h->laser.min_valid_points; a.L.scan_window = h->laser.scan_window;
+    a.L.flags = h->laser.flags;
     a.cs = h->d_cs;
     a.hashmat = h->d_hashmat;
     a.hash_chunk = h->hash_chunk;

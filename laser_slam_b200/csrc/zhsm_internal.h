@@ -64,6 +64,7 @@ struct LaserDev {
     float fi_min, dfi;
     int min_range_cm, max_range_cm;
     int min_valid_points, scan_window;
+    int flags;  // ZHSM_LASER_*
 };
 
 struct PlicpArgs {

@@ -9,6 +9,7 @@ static LaserDev laser_dev(const zhsm_handle *h) {
     L.n = h->laser.n; L.fi_min = h->laser.fi_min; L.dfi = h->laser.dfi;
     L.min_range_cm = h->laser.min_range_cm; L.max_range_cm = h->laser.max_range_cm;
     L.min_valid_points = h->laser.min_valid_points; L.scan_window = h->laser.scan_window;
+    L.flags = h->laser.flags;
     return L;
 }
 

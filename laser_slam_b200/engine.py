@@ -25,7 +25,7 @@ class ZhsmError(RuntimeError):
 class Laser(C.Structure):
     _fields_ = [("n", C.c_int32), ("fi_min", C.c_float), ("dfi", C.c_float), ("min_range_cm", C.c_int32),
                 ("max_range_cm", C.c_int32), ("min_valid_points", C.c_int32), ("scan_window", C.c_int32),
-                ("reserved", C.c_int32)]
+                ("flags", C.c_int32)]
 
 
 def laser_from_table(name, fi_min=None, max_range_cm=None):
@@ -69,6 +69,7 @@ SCANS_ON_DEVICE, JOBS_ON_DEVICE, RESULTS_ON_DEVICE, ALL_ON_DEVICE = 1, 2, 4, 7
 FILTER_SCANS, WRITEBACK_SCANS = 8, 16
 ALGO_PSM, ALGO_PM_ICP, ALGO_PSM_ICP, ALGO_FMATCH = 0, 1, 2, 3
 BEST_GOODNESS, BEST_MEAN_ERROR = 0, 1
+LASER_UTM_GATE = 1  # zhsm_laser.flags: pm_orientation_search's HOKUYO_UTM_30LX branch
 
 _lib = None
 

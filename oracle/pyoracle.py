@@ -164,6 +164,7 @@ def ref():
         _ref.zhpsm_ref_create.restype = C.c_void_p
         _ref.zhpsm_ref_create.argtypes = [C.c_char_p, C.c_float, C.c_int]
         _ref.zhpsm_ref_destroy.argtypes = [C.c_void_p]
+        _ref.zhpsm_ref_set_laser_name.argtypes = [C.c_void_p, C.c_char_p]
         _ref.zhpsm_ref_params.argtypes = [C.c_void_p] + [C.c_void_p] * 7
         _ref.zhpsm_ref_tables.argtypes = [C.c_void_p] * 4
         _ref.zhpsm_ref_preprocess.argtypes = [C.c_void_p] * 4
@@ -205,6 +206,10 @@ class RefPolarMatch:
                 self.h = None
         except Exception:
             pass
+
+    def set_laser_name(self, name):
+        """e.g. "HOKUYO_UTM_30LX": turns on the delta < PM_MAX_ERROR gate of pm_orientation_search (:1182-1191)."""
+        ref().zhpsm_ref_set_laser_name(self.h, name.encode())
 
     def tables(self):
         fi, si, co = (np.zeros(self.n, np.float32) for _ in range(3))

@@ -74,6 +74,12 @@ void *zhpsm_ref_create(const char *laser, float fi_min_override, int max_range_c
     h->n = m->m_pParam->pm_l_points;
     return h;
 }
+// pm_orientation_search keys one branch on the sensor's NAME (:1182-1191, "HOKUYO_UTM_30LX") although no parameter
+// table exists for it: renaming a ready matcher is the only way to execute that branch of the reference
+void zhpsm_ref_set_laser_name(void *hv, const char *name) {
+    Ref *h = (Ref *)hv;
+    h->m->m_pParam->pm_laser_name = std::string(name);
+}
 void zhpsm_ref_destroy(void *hv) {
     Ref *h = (Ref *)hv;
     if (!h) return;

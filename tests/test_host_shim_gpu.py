@@ -196,7 +196,9 @@ def test_reference_wrapper_unmodified_on_libzhsm(tmp_path, log, S, engine):
     p.do_compute_covariance = 1
     res = engine.plicp(scans, np.arange(S - 1), np.arange(1, S), params=p)
     okv = res["valid"] == 1
-    assert np.array_equal(outs[2][okv, 4:10], res["cov"][okv])
+    # (the covariance sums are FP64 shared-memory atomicAdds, whose order differs from launch to launch: 1e-6 relative,
+    # the tolerance of test_plicp_covariance_matches_oracle)
+    assert np.allclose(outs[2][okv, 4:10], res["cov"][okv], rtol=1e-6, atol=1e-12)
 
 
 def make_laser_local(g):

@@ -218,6 +218,25 @@ def test_compiled_reference_reproduces_zhpsm_goldens(log):
                 assert np.array_equal(pose, g[name + "_pose"][k]), (name, k)
 
 
+@pytest.mark.skipif(not po.have_ref(), reason="oracle/_ref not built (reference absent)")
+def test_compiled_reference_reproduces_utm_gate_goldens():
+    """tests/golden/utm_gate.npz = the compiled reference with pm_laser_name "HOKUYO_UTM_30LX" (the name switches on
+    the delta < PM_MAX_ERROR gate of pm_orientation_search, ZHPolar_Match.cpp:1182-1191); a subset re-run must
+    reproduce it bit for bit."""
+    import os
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "utm_gate.npz"))
+    g = load_log("fr079")
+    m = po.RefPolarMatch(g["laser_name"], fi_min=g["fi_min"], max_range_cm=int(g["max_range"]))
+    idx = np.linspace(0, g["scans"].shape[0] - 2, 30).astype(int)
+    pre = {k: m.preprocess(g["scans"][k]) for k in np.unique(np.concatenate([idx, idx + 1]))}
+    m.set_laser_name("HOKUYO_UTM_30LX")
+    for k in idx:
+        st, pose, _ = m.match(0, pre[k], pre[k + 1])
+        assert st == int(z["fr079_status"][k])
+        if st == 0:
+            assert np.array_equal(pose, z["fr079_pose"][k]), k
+
+
 # ---------------------------------------------------------------------------------------------------------------
 # zhicp oracle (oracle/icp_oracle.c): PARITY UNPINNED (MRPT 0.9.6 absent) -- pinned against regressions by the frozen
 # outputs on the reference's own wrapper-test clouds, and checked for the properties the algorithm must have.

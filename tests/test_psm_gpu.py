@@ -99,6 +99,33 @@ def test_matchers_vs_reference_goldens(engine, pre, log, name, algo):
     assert close[ok & st_eq].mean() >= 0.999
 
 
+@pytest.mark.parametrize("log", LOGS)
+def test_utm_gate_vs_reference_goldens(engine, pre, log):
+    """pm_orientation_search's HOKUYO_UTM_30LX branch (ZHPolar_Match.cpp:1182-1191; zhsm_laser.flags =
+    ZHSM_LASER_UTM_GATE): pm_psm of every consecutive pair, bit-identical to the compiled reference run with that
+    branch on (tests/golden/utm_gate.npz, tools/make_utm_goldens.py).  The gate changes > 90 % of the poses, so a
+    missing or misplaced gate cannot pass."""
+    import os
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "utm_gate.npz"))
+    g, r, bad, seg = pre(log)
+    lz = make_laser(g)
+    lz.flags = E.LASER_UTM_GATE
+    engine.set_laser(lz)
+    try:
+        S = r.shape[0]
+        res = engine.psm(r, bad, seg, np.arange(S - 1), np.arange(1, S), algo=E.ALGO_PSM)
+    finally:
+        engine.set_laser(make_laser(g))
+    want_pose, want_st = z[log + "_pose"], z[log + "_status"]
+    got_st = (res["status"] != 0).astype(np.int8)
+    assert np.array_equal(got_st, want_st), np.flatnonzero(got_st != want_st)[:10]
+    ok = want_st == 0
+    got = res["x"].astype(np.float32)
+    diff = np.flatnonzero(~(got.view(np.uint32) == want_pose.view(np.uint32)).all(1) & ok)
+    assert diff.size == 0, (log, diff[:10])
+    assert (np.any(want_pose != g["psm_pose"], 1)).mean() > 0.9   # the fixture really exercises the gate
+
+
 @pytest.mark.parametrize("log", ["intel-lab"])
 def test_fmatch_error_index(engine, pre, log):
     g, r, bad, seg = pre(log)
