@@ -134,6 +134,26 @@ zhsm_status zhsm_plicp_batch(zhsm_handle *h, const float *scans, int S, const in
                              const zhsm_plicp_params *params, zhsm_result *results, int16_t *corr_j1,
                              int16_t *corr_j2, unsigned flags, void *cuda_stream);
 
+/* zhsm_plicp_batch for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  NO COUNTERPART IN THE REFERENCE.
+ * Same kernels and same records as zhsm_plicp_batch, but it allocates nothing: every buffer is the CALLER'S DEVICE
+ * memory (d_scans [S][n] float cm, already median filtered; d_ref_idx / d_sens_idx [B]; d_first_guess [B][3] or NULL;
+ * d_results [B]; d_corr_j1 / d_corr_j2 [B][n] int16 or both NULL), and the kernels' scratch (jump tables, 8 bytes per
+ * ray and job, + a per-scan owner table) lives in one static device array of fixed size that every GPU loading the
+ * library holds until exit (8 MiB + 32 KiB).  Limits: B * beams <= ZHSM_NOALLOC_MAX_RAYS (970 jobs at 1080 beams, 512
+ * at 2048, 5793 at 181) and S <= ZHSM_NOALLOC_MAX_SCANS; beyond them the call fails with ZHSM_ERR_ARG and says so in
+ * zhsm_last_error.  zhsm_create / zhsm_set_laser (set-up, they do allocate) must have run; the first call on a device
+ * also resolves the array's address once (cudaGetSymbolAddress).  Asynchronous on cuda_stream (NULL = the handle's):
+ * the records are ready after zhsm_sync.  All calls on a device share the array, which keeps the last call's
+ * contents (nothing in it needs clearing: each launch re-initialises what it reads); calls that OVERLAP on the GPU --
+ * two streams, or two handles on one device -- race on it: keep them on one stream or order them with events. */
+#define ZHSM_NOALLOC_MAX_RAYS (1u << 20)
+#define ZHSM_NOALLOC_MAX_SCANS 8192
+zhsm_status zhsm_plicp_batch_noalloc(zhsm_handle *h, const float *d_scans, int S, const int32_t *d_ref_idx,
+                                     const int32_t *d_sens_idx, const double *d_first_guess, int B,
+                                     const zhsm_plicp_params *params, zhsm_result *d_results, int16_t *d_corr_j1,
+                                     int16_t *d_corr_j2, void *cuda_stream);
+
 /* ---- zhpsm: polar scan matching and pm_icp (src/zhpsm/ZHPolar_Match.cpp) ---------------------------------------
  * Scans are preprocessed once (zhsm_preprocess_batch) and then matched any number of times.  bad holds the
  * reference's PM_RANGE / PM_OCCLUDED / PM_EMPTY bit flags (PolarParameter.h:5-9) as uint8, seg the segment numbers of

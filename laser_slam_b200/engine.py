@@ -99,6 +99,7 @@ def load_library():
     L.zhsm_plicp_default_params.restype = None
     L.zhsm_median_filter_batch.argtypes = [vp, vp, i32, u32, vp]
     L.zhsm_plicp_batch.argtypes = [vp, vp, i32, vp, vp, vp, i32, C.POINTER(PlicpParams), vp, vp, vp, u32, vp]
+    L.zhsm_plicp_batch_noalloc.argtypes = [vp, vp, i32, vp, vp, vp, i32, C.POINTER(PlicpParams), vp, vp, vp, vp]
     L.zhsm_sync.argtypes = [vp, vp]
     L.zhsm_launch_count.argtypes = [vp]
     L.zhsm_launch_count.restype = C.c_uint64
@@ -220,6 +221,20 @@ class Engine:
         self._check(st, "zhsm_plicp_batch")
         if want_corr:
             return results, j1, j2
+        return results
+
+    def plicp_noalloc(self, scans, ref_idx, sens_idx, results, first_guess=None, params=None, corr_j1=None,
+                      corr_j2=None, stream=None):
+        """zhsm_plicp_batch_noalloc: every buffer is a CUDA tensor of the caller's; nothing is allocated (the kernels'
+        scratch is a static device array: B * beams <= 1 048 576, S <= 8192).  Asynchronous: sync() before reading."""
+        for a in (scans, ref_idx, sens_idx, results):
+            if not _is_dev(a):
+                raise ZhsmError("plicp_noalloc: scans, job lists and results must be device tensors")
+        st = self.L.zhsm_plicp_batch_noalloc(self.h, _ptr(scans), int(scans.shape[0]), _ptr(ref_idx), _ptr(sens_idx),
+                                             _ptr(first_guess), int(ref_idx.shape[0]),
+                                             C.byref(params) if params is not None else None, _ptr(results),
+                                             _ptr(corr_j1), _ptr(corr_j2), stream)
+        self._check(st, "zhsm_plicp_batch_noalloc")
         return results
 
     # ---- zhpsm family (CPolarMatch) -------------------------------------------------------------------------
