@@ -255,6 +255,37 @@ zhsm_status zhsm_available_area(zhsm_handle *h, const double *trans, const doubl
 zhsm_status zhsm_consensus(zhsm_handle *h, const double *poses, const float *good, const int32_t *set_off, int S,
                            uint8_t *keep, double *final_pose, int32_t *final_idx);
 
+/* ---- hand-over formats -----------------------------------------------------------------------
+ * covariance -> information, what the pose graph consumes from a matcher result: CMapNode::matchNodePairICP
+ * (src/mapGraph/MapNode.cpp:638-651) fills a symmetric 3x3 from getResult's six numbers cov6[k] = xx xy xt yy yt tt
+ * ((0,0) and (1,1) times `scale`, 1 in the reference) and sets information = covariance.inverse(); the loop-closure
+ * caller replaces it by the constant diag(const_diag) when m_bUseConstantCov (src/mapGraph/MapGraph.cpp:250-261,
+ * 1427-1429: m_cov_loopnode = diag(10,10,10)).  const_diag = NULL: the inverse; else the override.  info[k] is the
+ * row-major 3x3, ok[k] (may be NULL) = 0 where the covariance is singular (Eigen would return inf/NaN; so does info).
+ * Host arrays.  Also usable on zhsm_result.cov of PL-ICP (same six-number layout). */
+zhsm_status zhsm_cov_to_information(zhsm_handle *h, const double *cov6, int M, double scale, const double *const_diag,
+                                    double *info, uint8_t *ok);
+
+/* The client -> server frame record (src/tcp_slam/clientFrontend.cpp:300-305, 405-407 sendFrameInfo[Cov]; written by
+ * src/tcp_slam/clientLocal.cpp:189-199, parsed by src/tcp_slam/serverSocket.cpp:60-115): pose of the frame, the
+ * synchronisation number, optionally the six covariance numbers, and the np ranges of the scan [cm] -- a scan-pool row.
+ * zhsm_frame_pack writes one QDataStream block (big-endian: quint16 length, x y th as reals, qint32 syn, [6 doubles],
+ * quint16 np, np reals; a real is an 8-byte double, QDataStream's default since Qt 4.6, or 4 bytes with
+ * ZHSM_FRAME_QT_SINGLE) and returns its size (-1: does not fit cap / np > 65535 / block > 65535 bytes).
+ * zhsm_frame_unpack returns the bytes consumed, 0 when the buffer does not yet hold a whole block (the server waits
+ * for more, :69-74), -1 on a malformed block or np > cap_r.  Pure host code, no handle. */
+typedef struct zhsm_frame {
+    float x, y, th;  /* m, m, rad (curr_pose) */
+    int32_t syn;     /* syn_num */
+    int32_t np;      /* ranges that follow */
+    int32_t reserved;
+    double cov[6];   /* xx xy xt yy yt tt (USE_COV builds) */
+} zhsm_frame;
+#define ZHSM_FRAME_WITH_COV 1u
+#define ZHSM_FRAME_QT_SINGLE 2u
+long long zhsm_frame_pack(const zhsm_frame *f, const float *r, unsigned flags, uint8_t *buf, long long cap);
+long long zhsm_frame_unpack(const uint8_t *buf, long long len, unsigned flags, zhsm_frame *f, float *r, int cap_r);
+
 /* ---- submap cloud builder (src/mapGraph/MapNode.cpp:726-757 computePMAP + src/mapGraph/PMap.cpp) -------
  * Builds the point cloud zhicp aligns: K scans (scans[K][n] float cm, the handle's laser geometry) taken at traj[K][3]
  * (x, y, theta in the node frame, doubles like m_trajectory) are traced through a 5 cm hit/visit grid and the cells

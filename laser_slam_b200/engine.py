@@ -60,6 +60,46 @@ class IcpOptions(C.Structure):
                 ("kernel_rho", C.c_float), ("use_kernel", C.c_int32), ("Axy_aprox_derivatives", C.c_float)]
 
 
+class Frame(C.Structure):
+    """zhsm_frame: the client -> server frame record (src/tcp_slam/clientFrontend.cpp:300-305, 405-407)."""
+    _fields_ = [("x", C.c_float), ("y", C.c_float), ("th", C.c_float), ("syn", C.c_int32), ("np", C.c_int32),
+                ("reserved", C.c_int32), ("cov", C.c_double * 6)]
+
+
+FRAME_WITH_COV, FRAME_QT_SINGLE = 1, 2
+
+
+def frame_pack(x, y, th, syn, r, cov=None, single=False):
+    """One QDataStream block of the reference's TCP frame record (bytes)."""
+    L = load_library()
+    r = np.ascontiguousarray(r, np.float32)
+    f = Frame(float(x), float(y), float(th), int(syn), int(r.size), 0)
+    flags = (FRAME_WITH_COV if cov is not None else 0) | (FRAME_QT_SINGLE if single else 0)
+    if cov is not None:
+        for k in range(6):
+            f.cov[k] = float(cov[k])
+    buf = np.zeros(2 + 128 + 8 * r.size, np.uint8)
+    n = L.zhsm_frame_pack(C.byref(f), r.ctypes.data, flags, buf.ctypes.data, buf.size)
+    if n < 0:
+        raise ZhsmError("zhsm_frame_pack: frame does not fit a quint16-length block")
+    return buf[:n].tobytes()
+
+
+def frame_unpack(data, with_cov=False, single=False, cap=65535):
+    """-> (consumed bytes, dict) ; consumed 0 = incomplete block, raises on a malformed one."""
+    L = load_library()
+    buf = np.frombuffer(data, np.uint8)
+    r = np.zeros(cap, np.float32)
+    f = Frame()
+    flags = (FRAME_WITH_COV if with_cov else 0) | (FRAME_QT_SINGLE if single else 0)
+    n = L.zhsm_frame_unpack(buf.ctypes.data if buf.size else None, buf.size, flags, C.byref(f), r.ctypes.data, cap)
+    if n < 0:
+        raise ZhsmError("zhsm_frame_unpack: malformed frame block")
+    if n == 0:
+        return 0, None
+    return int(n), dict(x=f.x, y=f.y, th=f.th, syn=f.syn, r=r[:f.np].copy(), cov=np.array(list(f.cov)))
+
+
 RESULT_DTYPE = np.dtype([("x", "f8", 3), ("cov", "f8", 6), ("error", "f8"), ("valid", "i4"), ("iterations", "i4"),
                          ("nvalid", "i4"), ("status", "i4"), ("goodness", "f4"), ("quality", "f4"),
                          ("corr_hash", "u4"), ("n_loops", "i4"), ("reserved", "i4", 4)])
@@ -100,6 +140,11 @@ def load_library():
     L.zhsm_median_filter_batch.argtypes = [vp, vp, i32, u32, vp]
     L.zhsm_plicp_batch.argtypes = [vp, vp, i32, vp, vp, vp, i32, C.POINTER(PlicpParams), vp, vp, vp, u32, vp]
     L.zhsm_plicp_batch_noalloc.argtypes = [vp, vp, i32, vp, vp, vp, i32, C.POINTER(PlicpParams), vp, vp, vp, vp]
+    L.zhsm_cov_to_information.argtypes = [vp, vp, i32, C.c_double, vp, vp, vp]
+    L.zhsm_frame_pack.argtypes = [C.POINTER(Frame), vp, u32, vp, C.c_longlong]
+    L.zhsm_frame_pack.restype = C.c_longlong
+    L.zhsm_frame_unpack.argtypes = [vp, C.c_longlong, u32, C.POINTER(Frame), vp, i32]
+    L.zhsm_frame_unpack.restype = C.c_longlong
     L.zhsm_sync.argtypes = [vp, vp]
     L.zhsm_launch_count.argtypes = [vp]
     L.zhsm_launch_count.restype = C.c_uint64
@@ -138,6 +183,35 @@ def _is_dev(a):
     return hasattr(a, "data_ptr")
 
 
+_TORCH_DTYPES = {"float32": "torch.float32", "float64": "torch.float64", "int32": "torch.int32", "int16": "torch.int16",
+                 "uint8": "torch.uint8", "int8": "torch.int8"}
+
+
+def _check_dev(a, what, dtype, device, cols=None, rows=None):
+    """A device tensor gets the checks the numpy path makes: only its raw pointer crosses the boundary, so a sliced,
+    mistyped or misplaced tensor would otherwise be read as garbage (or fault the whole batch)."""
+    if a is None:
+        return
+    if not a.is_cuda:
+        raise ZhsmError(f"{what}: expected a CUDA tensor")
+    if a.device.index != device:
+        raise ZhsmError(f"{what}: tensor is on cuda:{a.device.index}, the engine's handle on cuda:{device}")
+    if str(a.dtype) != _TORCH_DTYPES[dtype]:
+        raise ZhsmError(f"{what}: dtype {a.dtype}, expected {dtype}")
+    if not a.is_contiguous():
+        raise ZhsmError(f"{what}: tensor must be contiguous")
+    if cols is not None and (a.dim() != 2 or a.shape[1] != cols):
+        raise ZhsmError(f"{what}: shape {tuple(a.shape)}, expected [*][{cols}]")
+    if rows is not None and a.shape[0] != rows:
+        raise ZhsmError(f"{what}: {a.shape[0]} rows, expected {rows}")
+
+
+def _same_side(what, *arrs):
+    sides = {_is_dev(a) for a in arrs if a is not None}
+    if len(sides) > 1:
+        raise ZhsmError(f"{what}: these arrays must all be host (numpy) or all device (torch) arrays")
+
+
 class Engine:
     """One handle = one GPU + one stream.  Mirrors the three matcher classes' batched form."""
 
@@ -149,6 +223,7 @@ class Engine:
             raise ZhsmError(f"zhsm_create(device={device}) failed with status {st}: no usable sm_100 GPU "
                             "(this engine has no CPU fallback)")
         self.h = h
+        self.device = int(device)
         self.laser = None
 
     def close(self):
@@ -179,7 +254,9 @@ class Engine:
         """In place.  numpy float32 [S][n] (host) or a CUDA tensor."""
         dev = _is_dev(scans)
         if not dev:
-            assert scans.dtype == np.float32 and scans.flags.c_contiguous
+            assert scans.dtype == np.float32 and scans.flags.c_contiguous and scans.shape[1] == self.laser.n
+        else:
+            _check_dev(scans, "median_filter: scans", "float32", self.device, cols=self.laser.n)
         S = scans.shape[0]
         self._check(self.L.zhsm_median_filter_batch(self.h, _ptr(scans), S, SCANS_ON_DEVICE if dev else 0, stream),
                     "zhsm_median_filter_batch")
@@ -196,8 +273,17 @@ class Engine:
         S = int(scans.shape[0])
         flags = (SCANS_ON_DEVICE if dev_scans else 0) | (JOBS_ON_DEVICE if dev_jobs else 0)
         flags |= (FILTER_SCANS if filter_scans else 0) | (WRITEBACK_SCANS if writeback else 0)
+        _same_side("plicp: ref_idx / sens_idx / first_guess", ref_idx, sens_idx, first_guess)
         if not dev_scans:
             assert scans.dtype == np.float32 and scans.flags.c_contiguous and scans.shape[1] == n
+        else:
+            _check_dev(scans, "plicp: scans", "float32", self.device, cols=n)
+        if dev_jobs:
+            _check_dev(ref_idx, "plicp: ref_idx", "int32", self.device)
+            _check_dev(sens_idx, "plicp: sens_idx", "int32", self.device, rows=B)
+            _check_dev(first_guess, "plicp: first_guess", "float64", self.device, cols=3, rows=B)
+        if results is not None and _is_dev(results):
+            _check_dev(results, "plicp: results", "uint8", self.device, cols=128, rows=B)
         if not dev_jobs:
             ref_idx = np.ascontiguousarray(ref_idx, np.int32)
             sens_idx = np.ascontiguousarray(sens_idx, np.int32)
@@ -230,6 +316,14 @@ class Engine:
         for a in (scans, ref_idx, sens_idx, results):
             if not _is_dev(a):
                 raise ZhsmError("plicp_noalloc: scans, job lists and results must be device tensors")
+        B, n = int(ref_idx.shape[0]), self.laser.n
+        _check_dev(scans, "plicp_noalloc: scans", "float32", self.device, cols=n)
+        _check_dev(ref_idx, "plicp_noalloc: ref_idx", "int32", self.device)
+        _check_dev(sens_idx, "plicp_noalloc: sens_idx", "int32", self.device, rows=B)
+        _check_dev(first_guess, "plicp_noalloc: first_guess", "float64", self.device, cols=3, rows=B)
+        _check_dev(results, "plicp_noalloc: results", "uint8", self.device, cols=128, rows=B)
+        _check_dev(corr_j1, "plicp_noalloc: corr_j1", "int16", self.device, cols=n, rows=B)
+        _check_dev(corr_j2, "plicp_noalloc: corr_j2", "int16", self.device, cols=n, rows=B)
         st = self.L.zhsm_plicp_batch_noalloc(self.h, _ptr(scans), int(scans.shape[0]), _ptr(ref_idx), _ptr(sens_idx),
                                              _ptr(first_guess), int(ref_idx.shape[0]),
                                              C.byref(params) if params is not None else None, _ptr(results),
@@ -263,6 +357,19 @@ class Engine:
         dev_jobs = _is_dev(ref_idx)
         B, S = int(ref_idx.shape[0]), int(scans.shape[0])
         flags = (SCANS_ON_DEVICE if dev else 0) | (JOBS_ON_DEVICE if dev_jobs else 0)
+        _same_side("psm: scans / bad / seg", scans, bad, seg)
+        _same_side("psm: ref_idx / act_idx / init_pose", ref_idx, act_idx, init_pose)
+        n = self.laser.n
+        if dev:
+            _check_dev(scans, "psm: scans", "float32", self.device, cols=n)
+            _check_dev(bad, "psm: bad", "uint8", self.device, cols=n, rows=S)
+            _check_dev(seg, "psm: seg", "int16", self.device, cols=n, rows=S)
+        if dev_jobs:
+            _check_dev(ref_idx, "psm: ref_idx", "int32", self.device)
+            _check_dev(act_idx, "psm: act_idx", "int32", self.device, rows=B)
+            _check_dev(init_pose, "psm: init_pose", "float32", self.device, cols=3, rows=B)
+        if results is not None and _is_dev(results):
+            _check_dev(results, "psm: results", "uint8", self.device, cols=128, rows=B)
         if not dev_jobs:
             ref_idx = np.ascontiguousarray(ref_idx, np.int32)
             act_idx = np.ascontiguousarray(act_idx, np.int32)
@@ -314,6 +421,15 @@ class Engine:
         off = np.ascontiguousarray(off, np.int32)
         cnt = np.ascontiguousarray(cnt, np.int32)
         flags = (SCANS_ON_DEVICE if _is_dev(pts) else 0) | (JOBS_ON_DEVICE if _is_dev(ref_idx) else 0)
+        _same_side("icp: ref_idx / cur_idx / init", ref_idx, cur_idx, init)
+        if _is_dev(pts):
+            _check_dev(pts, "icp: pts", "float32", self.device)
+        if _is_dev(ref_idx):
+            _check_dev(ref_idx, "icp: ref_idx", "int32", self.device)
+            _check_dev(cur_idx, "icp: cur_idx", "int32", self.device, rows=int(ref_idx.shape[0]))
+            _check_dev(init, "icp: init", "float64", self.device, cols=3, rows=int(ref_idx.shape[0]))
+        if results is not None and _is_dev(results):
+            _check_dev(results, "icp: results", "uint8", self.device, cols=128, rows=int(ref_idx.shape[0]))
         if not _is_dev(pts):
             pts = np.ascontiguousarray(pts, np.float32)
         if not _is_dev(ref_idx):
@@ -374,6 +490,17 @@ class Engine:
         self._check(self.L.zhsm_consensus(self.h, _ptr(poses), _ptr(good), _ptr(set_off), S, _ptr(keep), _ptr(fp), _ptr(fi)),
                     "zhsm_consensus")
         return keep, fp, fi
+
+    def cov_to_information(self, cov6, scale=1.0, const_diag=None):
+        """matchNodePairICP's information = covariance.inverse() (MapNode.cpp:638-651), or the constant override
+        (MapGraph.cpp:1427-1429) when const_diag is given: -> (info [M][3][3], ok [M])."""
+        cov6 = np.ascontiguousarray(cov6, np.float64).reshape(-1, 6)
+        M = cov6.shape[0]
+        info = np.zeros((M, 3, 3)); ok = np.zeros(M, np.uint8)
+        cd = None if const_diag is None else np.ascontiguousarray(const_diag, np.float64)
+        self._check(self.L.zhsm_cov_to_information(self.h, _ptr(cov6), M, float(scale), _ptr(cd), _ptr(info), _ptr(ok)),
+                    "zhsm_cov_to_information")
+        return info, ok
 
     def submap_cloud(self, scans_cm, traj, cap=1 << 20):
         """CMapNode::computePMAP: occupied 5 cm cells of K scans taken at traj [K][3]; returns (x, y, grid dims)."""

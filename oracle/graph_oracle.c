@@ -137,3 +137,27 @@ void orc_consensus(const double *poses, const float *good, const int32_t *set_of
         }
     }
 }
+
+/* Eigen/src/LU/InverseImpl.h, compute_inverse<MatrixType, ResultType, 3>: cofactors of column 0, det = their dot
+ * product with column 0 (redux order a0 + (a1 + a2)), inverse(i,j) = cofactor(j,i) / det. */
+static double cof3(const double m[9], int i, int j) {
+    int i1 = (i + 1) % 3, i2 = (i + 2) % 3, j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+    return m[3 * i1 + j1] * m[3 * i2 + j2] - m[3 * i1 + j2] * m[3 * i2 + j1];
+}
+void orc_cov_to_information(const double *cov6, int M, double scale, const double *const_diag, double *info) {
+    for (int k = 0; k < M; k++) {
+        const double *c = cov6 + 6 * (size_t)k;
+        double *o = info + 9 * (size_t)k;
+        if (const_diag) {
+            for (int q = 0; q < 9; q++) o[q] = 0.0;
+            o[0] = const_diag[0]; o[4] = const_diag[1]; o[8] = const_diag[2];
+            continue;
+        }
+        double m[9] = {c[0] * scale, c[1], c[2], c[1], c[3] * scale, c[4], c[2], c[4], c[5]};
+        double c00 = cof3(m, 0, 0), c10 = cof3(m, 1, 0), c20 = cof3(m, 2, 0);
+        double det = c00 * m[0] + (c10 * m[3] + c20 * m[6]);
+        double invdet = 1.0 / det;
+        for (int i = 0; i < 3; i++)
+            for (int j = 0; j < 3; j++) o[3 * i + j] = cof3(m, j, i) * invdet;
+    }
+}

@@ -19,6 +19,10 @@ void orc_available_area(const double *trans, const double *cov_xy, int M, uint8_
  * final_idx[s] = entry (absolute index) closest to it, -1 for an empty set. */
 void orc_consensus(const double *poses, const float *good, const int32_t *set_off, int S, uint8_t *keep,
                    double *final_pose, int32_t *final_idx);
+/* matchNodePairICP's hand-over (src/mapGraph/MapNode.cpp:638-651): symmetric 3x3 from cov6 = xx xy xt yy yt tt
+ * ((0,0), (1,1) times scale), information = covariance.inverse() by Eigen's 3x3 cofactor formula; const_diag != NULL:
+ * the m_bUseConstantCov override (src/mapGraph/MapGraph.cpp:250-261,1427-1429).  info = row-major 3x3 per record. */
+void orc_cov_to_information(const double *cov6, int M, double scale, const double *const_diag, double *info);
 #ifdef __cplusplus
 }
 #endif

@@ -378,6 +378,18 @@ def consensus(poses, good, set_off):
     return keep, fp, fi
 
 
+def cov_to_information(cov6, scale=1.0, const_diag=None):
+    """matchNodePairICP's information = covariance.inverse() (Eigen 3x3 cofactor formula), or the constant override."""
+    cov6 = np.ascontiguousarray(cov6, np.float64).reshape(-1, 6)
+    info = np.zeros((cov6.shape[0], 3, 3))
+    cd = None if const_diag is None else np.ascontiguousarray(const_diag, np.float64)
+    L = lib()
+    L.orc_cov_to_information.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_void_p, C.c_void_p]
+    L.orc_cov_to_information(cov6.ctypes.data, cov6.shape[0], float(scale), None if cd is None else cd.ctypes.data,
+                             info.ctypes.data)
+    return info
+
+
 def ref_oplus_point(pose, pt):
     """OrientedPoint2D::oplus(Point2D) executed by the compiled reference (src/zhpsm/point.cpp:63-69)."""
     R = ref()

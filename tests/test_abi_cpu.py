@@ -200,3 +200,47 @@ def test_csm_entry_plain_c_links_against_libzhsm_only(lib, tmp_path):
         assert b"no usable sm_100 GPU" in r.stderr
     needed = subprocess.run(["readelf", "-d", str(exe)], capture_output=True).stdout.decode()
     assert "libzhsm.so" in needed and "csm" not in needed.replace("libzhsm", "").lower()
+
+
+def test_frame_record_wire_format(lib):
+    """the client -> server frame record as clientLocal.cpp:189-199 writes it and serverSocket.cpp:60-115
+    parses it (QDataStream: big-endian, quint16 block length, reals as 8-byte doubles since Qt 4.6).  A hand-built
+    byte vector pins the layout; round trips cover both precisions, with and without covariance, and the server's
+    "wait for more bytes" rule."""
+    import struct
+    from laser_slam_b200 import engine as E
+    r = np.array([123.0, 4567.5, 5001.0], np.float32)
+    cov = [1e-4, 2e-5, -3e-6, 4e-4, 5e-6, 6e-3]
+    blk = E.frame_pack(1.5, -2.25, 0.125, 42, r, cov=cov)
+    want = struct.pack(">dddi", 1.5, -2.25, 0.125, 42) + struct.pack(">6d", *cov) + struct.pack(">H", 3) + \
+        struct.pack(">3d", 123.0, 4567.5, 5001.0)
+    assert blk == struct.pack(">H", len(want)) + want
+    blk_nc = E.frame_pack(1.5, -2.25, 0.125, 42, r)
+    want_nc = struct.pack(">dddi", 1.5, -2.25, 0.125, 42) + struct.pack(">H", 3) + struct.pack(">3d", 123.0, 4567.5, 5001.0)
+    assert blk_nc == struct.pack(">H", len(want_nc)) + want_nc
+    blk_s = E.frame_pack(1.5, -2.25, 0.125, 42, r, single=True)
+    want_s = struct.pack(">fffi", 1.5, -2.25, 0.125, 42) + struct.pack(">H", 3) + struct.pack(">3f", 123.0, 4567.5, 5001.0)
+    assert blk_s == struct.pack(">H", len(want_s)) + want_s
+    # round trips on real scans (LMS151-sized, 541 beams: the sensor the TCP client was written for)
+    rng = np.random.default_rng(1)
+    for single in (False, True):
+        for with_cov in (False, True):
+            scan = rng.uniform(10, 5001, 541).astype(np.float32)
+            c = rng.normal(0, 1e-3, 6) if with_cov else None
+            b = E.frame_pack(3.25, 7.5, -1.0, 7, scan, cov=c, single=single)
+            n, f = E.frame_unpack(b + b"tail", with_cov=with_cov, single=single)
+            assert n == len(b) and f["syn"] == 7 and (f["x"], f["y"], f["th"]) == (3.25, 7.5, -1.0)
+            assert np.array_equal(f["r"], scan)
+            if with_cov:
+                assert np.array_equal(f["cov"], c)
+            # a block that has not arrived completely: the server waits (consumed = 0), whatever the cut
+            for cut in (0, 1, 2, len(b) // 2, len(b) - 1):
+                assert E.frame_unpack(b[:cut], with_cov=with_cov, single=single)[0] == 0
+    # a frame whose block would not fit the quint16 length field is refused, like the reference's format cannot say it
+    with pytest.raises(zh.ZhsmError):
+        E.frame_pack(0, 0, 0, 0, np.zeros(9000, np.float32))
+    # a malformed block (np says more ranges than the block holds)
+    bad = bytearray(E.frame_pack(0, 0, 0, 0, np.ones(4, np.float32)))
+    bad[2 + 28 + 1] = 200
+    with pytest.raises(zh.ZhsmError):
+        E.frame_unpack(bytes(bad))

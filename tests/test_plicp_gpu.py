@@ -285,3 +285,33 @@ def test_bad_device_job_index_fails_its_own_job_only():
     rest = np.setdiff1d(np.arange(64), badj)
     assert np.array_equal(a[rest].tobytes(), b[rest].tobytes())
     eng.close()
+
+
+def test_engine_rejects_malformed_device_tensors():
+    """Only raw pointers cross the C ABI, so the binding must refuse what the kernels would misread: a float64 or
+    sliced scan tensor, job arrays split between host and device, a wrong beam count."""
+    import torch
+    import laser_slam_b200 as zh
+    g = load_log("fr079")
+    eng = zh.Engine(0)
+    eng.set_laser(make_laser(g))
+    dev = torch.device("cuda:0")
+    scans = torch.from_numpy(g["scans"][:9].copy()).to(dev)
+    ri = torch.arange(0, 8, dtype=torch.int32, device=dev)
+    res = torch.zeros((8, 128), dtype=torch.uint8, device=dev)
+    bad_calls = [
+        lambda: eng.plicp(scans.double(), ri, ri + 1, results=res),               # dtype
+        lambda: eng.plicp(scans[:, :360], ri, ri + 1, results=res),               # sliced: not contiguous, wrong beams
+        lambda: eng.plicp(scans, ri, (ri + 1).cpu().numpy(), results=res),        # job arrays on two sides
+        lambda: eng.plicp(scans, ri, ri + 1, first_guess=np.zeros((8, 3)), results=res),  # first_guess on the host
+        lambda: eng.plicp(scans, ri.long(), ri + 1, results=res),                 # int64 indices
+        lambda: eng.plicp(scans, ri, ri + 1, results=res[:4]),                    # too few result records
+        lambda: eng.median_filter(scans.t().contiguous()),                        # [n][S] instead of [S][n]
+    ]
+    for k, call in enumerate(bad_calls):
+        with pytest.raises(zh.ZhsmError):
+            call()
+    eng.plicp(scans, ri, ri + 1, results=res)   # and the well-formed call still runs
+    eng.sync()
+    assert (res.cpu().numpy().view(zh.RESULT_DTYPE).reshape(-1)["valid"] == 1).all()
+    eng.close()
