@@ -54,3 +54,39 @@ def guesses(nodes, cand, G=8, seed=20261104):
         init[k] = gt + rng.normal(0, 1, (G, 3)) * [0.15, 0.15, np.deg2rad(5)]
         init[k, 0] = gt
     return init
+
+
+# ---- BASELINE config 3 exactly as SURVEY 8d states it -----------------------------------------------------------------
+C3_SEED, C3_G = 20261104, 64
+
+
+def pairs_c3(nodes, flags, adj_win=2):
+    """Config 3's pair list: the consecutive node pairs (k, k+1) plus the loop candidates (GT poses within 2 m =
+    isLoopyArea, bbox overlap >= 0.4 = isOverlappedArea, outside the adjacency window).  Rows are (cur, ref)."""
+    N = len(nodes)
+    consec = np.stack([np.arange(1, N), np.arange(0, N - 1)], 1).astype(np.int32)
+    return np.concatenate([consec, candidates(flags, adj_win)]).astype(np.int32)
+
+
+def guesses_c3(nodes, pairs, G=C3_G, seed=C3_SEED):
+    """64 initial guesses per pair: guess 0 = the GT relative pose, guesses 1..63 = guess 0 (+) U(+-0.5 m, +-0.5 m,
+    +-15 deg), Philox key = seed, counter = pair * 64 + g."""
+    init = np.zeros((len(pairs), G, 3))
+    half = np.array([0.5, 0.5, np.deg2rad(15.0)])
+    for k, (i, j) in enumerate(pairs):
+        gt = rel_pose(nodes[j]["root"], nodes[i]["root"])
+        init[k, 0] = gt
+        for gidx in range(1, G):
+            u = np.random.Generator(np.random.Philox(key=seed, counter=[k * G + gidx, 0, 0, 0])).uniform(-1.0, 1.0, 3)
+            init[k, gidx] = oplus(gt, u * half)
+    return init
+
+
+def build_c3(g, clouds_of, gate, K=15, stride=5, max_nodes=400):
+    """nodes -> clouds (clouds_of(node) -> (x, y)) -> node table -> gate(pose, ld, ru, cur) -> pairs + guesses."""
+    nodes = make_nodes(g, K=K, stride=stride, max_nodes=max_nodes)
+    clouds = [clouds_of(nd) for nd in nodes]
+    pose, ld, ru = node_table(nodes, clouds)
+    flags = gate(pose, ld, ru, np.arange(len(nodes)))
+    pairs = pairs_c3(nodes, flags)
+    return nodes, clouds, pose, flags, pairs, guesses_c3(nodes, pairs)

@@ -5,6 +5,7 @@
   * device-pointer path == host-pointer path through the C ABI on a slice;
   * the recovered poses agree with the generator's ground truth (the noise floor of 1 cm range noise);
   * a sample of the batch still agrees with the CPU oracle (the parity bar proper)."""
+import os
 import zlib
 
 import numpy as np
@@ -62,9 +63,10 @@ def test_plicp_one_million_pairs(engine):
     g = r[idx]
     d = np.abs(g["x"] - o["x"])
     assert (g["valid"] == o["valid"]).all()
-    assert ((d[:, 0] <= 1e-4) & (d[:, 1] <= 1e-4) & (d[:, 2] <= 1e-5)).mean() >= 0.998
-    assert (g["iterations"] == o["iterations"]).mean() >= 0.998
-    assert (g["corr_hash"] == o["corr_hash"]).mean() >= 0.998
+    bad = ~((d[:, 0] <= 1e-4) & (d[:, 1] <= 1e-4) & (d[:, 2] <= 1e-5)) | (g["iterations"] != o["iterations"]) | \
+        (g["corr_hash"] != o["corr_hash"])
+    print("C4 sample of 512 pairs: differing from the oracle:", idx[bad].tolist())
+    assert bad.sum() == 0, idx[bad].tolist()   # measured 99.999 % on 100 000 pairs: a 512-pair sample has none
 
 
 def test_icp_quarter_million_jobs(engine):
@@ -103,4 +105,37 @@ def test_icp_quarter_million_jobs(engine):
     g = r.reshape(-1)[idx]
     dp = np.abs(g["x"] - o["pose"])
     ok = (dp[:, 0] <= 1e-4) & (dp[:, 1] <= 1e-4) & (dp[:, 2] <= 1e-5) & (g["iterations"] == o["nIterations"])
-    assert ok.mean() >= 0.98, ok.mean()
+    assert ok.all(), idx[~ok].tolist()[:20]   # equal to the oracle on every job
+
+
+def test_c4_parity_on_ten_thousand_pairs(engine):
+    """north_star's parity bar on the headline workload itself (SURVEY 8d C4: synthetic 1080-beam pairs, bench.py's
+    generator and seed): 10 000 pairs against the CPU restatement -- valid flags equal, poses within 1e-4 m / 1e-5 rad,
+    iteration counts and correspondence hashes equal on >= 99.9 %; the pairs that differ are listed (measured: 1 in
+    100 000, a floating-point near-tie)."""
+    import torch
+    import bench
+    import laser_slam_b200 as zh
+    lz = bench.make_laser(zh)
+    engine.set_laser(lz)
+    dev = torch.device("cuda:0")
+    P, n = 10_000, lz.n
+    scans = torch.empty((2 * P, n), dtype=torch.float32, device=dev)
+    truth = torch.empty((P, 3), dtype=torch.float64, device=dev)
+    engine.synth_pairs(scans, truth, 500_000, P, seed=bench.SEED)   # pairs from the middle of the 1 M batch
+    engine.median_filter(scans)
+    ri = torch.arange(0, 2 * P, 2, dtype=torch.int32, device=dev)
+    res = torch.zeros((P, 128), dtype=torch.uint8, device=dev)
+    engine.plicp(scans, ri, ri + 1, results=res)
+    engine.sync()
+    r = res.cpu().numpy().view(zh.RESULT_DTYPE).reshape(-1)
+    h = scans.cpu().numpy()
+    o = po.zhcsm_fmatch_batch(h, np.arange(0, 2 * P, 2), np.arange(1, 2 * P, 2), lz.fi_min, lz.dfi, lz.min_range_cm,
+                              lz.max_range_cm, nthreads=os.cpu_count() or 8)
+    assert np.array_equal(r["valid"], o["valid"])
+    both = r["valid"] == 1
+    d = np.abs(r["x"] - o["x"])
+    bad = (~((d[:, 0] <= 1e-4) & (d[:, 1] <= 1e-4) & (d[:, 2] <= 1e-5)) & both) | (r["iterations"] != o["iterations"]) | \
+        ((r["corr_hash"] != o["corr_hash"]) & both) | ((r["nvalid"] != o["nvalid"]) & both)
+    print(f"C4 parity: {int(bad.sum())} of {P} pairs differ from the oracle: {np.flatnonzero(bad).tolist()[:20]}")
+    assert bad.mean() <= 0.001, np.flatnonzero(bad).tolist()[:20]

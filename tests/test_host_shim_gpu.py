@@ -40,7 +40,7 @@ def test_shim_matches_goldens(tmp_path, log, S):
         d = np.abs(out[:, 1:] - want)
         ok = (d[:, 0] <= 1e-2 + 1e-5 * np.abs(want[:, 0])) & (d[:, 1] <= 1e-2 + 1e-5 * np.abs(want[:, 1])) & (d[:, 2] <= 1e-5)
         ok_all.append(ok.mean())
-        assert ok.mean() >= 0.995, (mode, ok.mean())   # 1e-4 m = 1e-2 cm
+        assert (~ok).sum() <= _golden_mismatch_budget(log), (mode, np.flatnonzero(~ok).tolist())   # 1e-4 m = 1e-2 cm
     print(log, "shim pose agreement per mode", ok_all)
 
 

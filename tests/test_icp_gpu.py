@@ -59,7 +59,7 @@ def test_reference_node_pairs_golden(eng, nodes):
     for init, gold in ((d["init"], d["oracle"]), (np.zeros_like(d["init"]), d["oracle_zero_init"])):
         r = eng.icp(d["pts"], d["off"], d["cnt"], d["pairs"][:, 0], d["pairs"][:, 1], init)
         assert r["valid"].all()
-        _compare(r, gold, pose_frac=0.95, iter_frac=0.95)
+        _compare(r, gold, pose_frac=1.0, iter_frac=1.0)
 
 
 def test_against_live_oracle_multistart(eng, nodes):
@@ -76,7 +76,7 @@ def test_against_live_oracle_multistart(eng, nodes):
     ci = np.repeat(d["pairs"][:, 1], G)
     o = po.mrpt_icp_batch(d["pts"], d["off"], d["cnt"], ri, ci, init, nthreads=os.cpu_count() or 4)
     r = eng.icp(d["pts"], d["off"], d["cnt"], ri, ci, init)
-    _compare(r, o, pose_frac=0.97, iter_frac=0.97)
+    _compare(r, o, pose_frac=1.0, iter_frac=1.0)
     # best-of-G on the device == the host rule (highest goodness, then lowest error, then lowest index)
     best, rec = eng.best_of_starts(r, P, G)
     rr = r.reshape(P, G)
@@ -103,7 +103,7 @@ def test_options_and_edge_cases(eng, nodes):
         go = eng.default_icp_options(**over)
         o = po.mrpt_icp_batch(d["pts"], d["off"], d["cnt"], pr[:, 0], pr[:, 1], d["init"][:16], oo)
         r = eng.icp(d["pts"], d["off"], d["cnt"], pr[:, 0], pr[:, 1], d["init"][:16], options=go)
-        _compare(r, o, pose_frac=0.9, iter_frac=0.9)
+        _compare(r, o, pose_frac=1.0, iter_frac=1.0)
     # disjoint clouds: bounding boxes do not touch -> no correspondences, one iteration, pose untouched, goodness 1
     x = np.linspace(0, 1, 50, dtype=np.float32)
     pts, off, cnt = po.pack_clouds([(x, x * 0), (x + 100, x * 0), (x[:1], x[:1]), (x[:0], x[:0])])
@@ -128,3 +128,26 @@ def test_argument_errors(eng):
         eng.icp(pts, [2], [4], [0], [0])          # table runs past the pool
     with pytest.raises(ZhsmError):
         eng.icp(pts, [0], [4], [0], [0], options=eng.default_icp_options(ALFA=1.0))
+
+
+def test_reference_embedded_scans_from_test_cpp(eng):
+    """The one remaining indirect pin the tree offers for zhicp: src/zhicp/test.cpp:54-60 embeds two 361-beam scans
+    (SCAN_RANGES_1/2, SCAN_VALID_1/2) and runs CICP::Align from (0.8, 0, 0) (:112) with exactly the options of
+    CICPWarpper::initICP.  The inputs are reference-held (tests/golden/zhicp_testcpp.npz,
+    tools/make_icp_testcpp_fixture.py); the tree records no output, so parity stays unpinned: CUDA == restatement, and
+    the result is the small correction of the 0.8 m start that the two scans visibly need."""
+    from oracle import pyoracle as po
+    z = np.load(os.path.join(ROOT, "tests", "golden", "zhicp_testcpp.npz"))
+    th = -np.pi / 2 + np.arange(361) * (np.pi / 360)   # aperture pi, right to left (test.cpp:73-75)
+
+    def cloud(r, v):
+        ok = v != 0
+        return (r[ok] * np.cos(th[ok])).astype(np.float32), (r[ok] * np.sin(th[ok])).astype(np.float32)
+    pts, off, cnt = po.pack_clouds([cloud(z["scan_ranges_1"], z["scan_valid_1"]), cloud(z["scan_ranges_2"], z["scan_valid_2"])])
+    init = z["initial_pose"][None]
+    for dec in (5, 1):
+        o = po.mrpt_icp_batch(pts, off, cnt, [0], [1], init, po.icp_default_options(corresponding_points_decimation=dec))
+        r = eng.icp(pts, off, cnt, np.array([0]), np.array([1]), init, options=eng.default_icp_options(corresponding_points_decimation=dec))
+        _compare(r, o)
+        assert r["valid"][0] == 1 and r["goodness"][0] > 0.95
+        assert abs(r["x"][0, 0] - 0.8) < 0.05 and abs(r["x"][0, 1]) < 0.15 and abs(np.rad2deg(r["x"][0, 2]) - 9.0) < 1.5

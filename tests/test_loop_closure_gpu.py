@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 
 from oracle import pyoracle as po
-from tests.loop_cases import candidates, guesses, make_nodes, node_table, oplus, rel_pose
+from tests.loop_cases import candidates, guesses, make_nodes, node_table, oplus, rel_pose  # noqa: F401
 from tests.support import load_log, make_laser
 
 pytestmark = pytest.mark.gpu
@@ -41,7 +41,7 @@ def test_loop_closure_pipeline(engine, log):
     o = po.mrpt_icp_batch(pts, off, cnt, ri, ci, init, nthreads=8)
     dp = np.abs(r["x"] - o["pose"])
     ok = (dp[:, 0] <= 1e-4) & (dp[:, 1] <= 1e-4) & (dp[:, 2] <= 1e-5) & (r["iterations"] == o["nIterations"])
-    assert ok.mean() >= 0.98, (ok.mean(), dp.max(0))
+    assert ok.all(), (np.flatnonzero(~ok)[:20], dp.max(0))   # equal to the oracle on every job
     assert np.allclose(r["goodness"][ok], o["goodness"][ok], atol=1e-6)
     best, rec = engine.best_of_starts(r, len(cand), G)
     # 4. acceptance + isAvaliableArea + consensus, per new node, from the GPU's own ICP results
@@ -66,3 +66,40 @@ def test_loop_closure_pipeline(engine, log):
     # sanity against ground truth: accepted loop closures put the new node where the log says it is
     err = np.hypot(*(fp[:, :2] - pose[cur_nodes, :2]).T)
     assert np.median(err) < 0.15, err
+
+
+def test_config3_mit_cscail_64_guesses(engine):
+    """BASELINE config 3 as stated: zhicp loop-closure candidates on data/mit-cscail.log, 64 initial guesses per pair
+    (consecutive node pairs + candidates within 2 m / bbox overlap >= 0.4, guess 0 = GT relative pose,
+    guesses 1..63 = guess 0 (+) U(+-0.5 m, +-0.5 m, +-15 deg), Philox seed 20261104, counter = pair * 64 + g).
+    The call path it stands for: CMapNode::matchNodePairICP (src/mapGraph/MapNode.cpp:625-655) from
+    CMapGraph::addMapNode (src/mapGraph/MapGraph.cpp:1382-1383).  Every (pair, guess) job against the CPU
+    restatement; the best start per pair must put the node where the log's ground truth says."""
+    from tests.loop_cases import C3_G, build_c3
+    g = load_log("mit-cscail")
+    engine.set_laser(make_laser(g))
+    nodes, clouds, pose, flags, pairs, init = build_c3(
+        g, lambda nd: engine.submap_cloud(nd["scans"], nd["traj"])[:2], engine.gate_candidates)
+    assert np.array_equal(flags, po.gate_candidates(pose, *node_table(nodes, clouds)[1:], np.arange(len(nodes))))
+    n_loop = len(pairs) - (len(nodes) - 1)
+    assert len(nodes) >= 200 and n_loop >= 40, (len(nodes), n_loop)
+    pts, off, cnt = po.pack_clouds(clouds)
+    ri, ci = np.repeat(pairs[:, 1], C3_G), np.repeat(pairs[:, 0], C3_G)
+    jobs = init.reshape(-1, 3)
+    r = engine.icp(pts, off, cnt, ri, ci, jobs)
+    o = po.mrpt_icp_batch(pts, off, cnt, ri, ci, jobs, nthreads=16)
+    dp = np.abs(r["x"] - o["pose"])
+    bad = ~((dp[:, 0] <= 1e-4) & (dp[:, 1] <= 1e-4) & (dp[:, 2] <= 1e-5) & (r["iterations"] == o["nIterations"]) &
+            (r["nvalid"] == o["nCorrespondences"]))
+    print(f"\nconfig 3: {len(nodes)} nodes, {len(pairs)} pairs ({n_loop} loop candidates) x {C3_G} = {jobs.shape[0]} jobs; "
+          f"jobs differing from the oracle: {np.flatnonzero(bad).tolist()[:20]}")
+    assert bad.sum() == 0, np.flatnonzero(bad)[:20]
+    assert np.allclose(r["goodness"], o["goodness"], atol=1e-6)
+    best, rec = engine.best_of_starts(r, len(pairs), C3_G)
+    assert (best == 0).mean() < 0.9 and (best >= 0).all()     # the other 63 starts matter
+    # against ground truth: the preferred start recovers the GT relative pose of the pair
+    gt = init[:, 0]
+    err = np.abs(rec["x"] - gt)
+    acc = rec["goodness"] >= 0.8
+    assert acc.mean() > 0.5
+    assert np.median(np.hypot(err[acc, 0], err[acc, 1])) < 0.10 and np.median(err[acc, 2]) < np.deg2rad(1.5)

@@ -125,13 +125,19 @@ def _oracle(g, scans, ri, si, first_guess=None):
                                  first_guess=first_guess, nthreads=8)
 
 
-def _assert_same_as_oracle(res, o, min_frac=0.999):
+def _assert_same_as_oracle(res, o, min_frac=0.999, max_bad=None):
+    """north_star: poses within 1e-4 m / 1e-5 rad, iteration counts equal, correspondences >= 99.9 % identical.  The
+    jobs that differ (documented floating-point near-ties) are listed by index; max_bad bounds their NUMBER
+    where the batch is too small for a fraction to mean anything."""
     assert np.array_equal(res["valid"], o["valid"])
     both = (res["valid"] == 1) & (o["valid"] == 1)
-    assert (pose_close(res["x"], o["x"]) | ~both).mean() >= min_frac
-    assert (res["iterations"] == o["iterations"]).mean() >= min_frac
-    assert ((res["corr_hash"] == o["corr_hash"]) | ~both).mean() >= min_frac
-    assert ((res["nvalid"] == o["nvalid"]) | ~both).mean() >= min_frac
+    bad = ~(pose_close(res["x"], o["x"]) | ~both) | (res["iterations"] != o["iterations"]) | \
+        ((res["corr_hash"] != o["corr_hash"]) & both) | ((res["nvalid"] != o["nvalid"]) & both)
+    idx = np.flatnonzero(bad)
+    print(f"jobs differing from the oracle: {idx.size} of {bad.size}: {idx.tolist()[:20]}")
+    if max_bad is not None:
+        assert idx.size <= max_bad, idx.tolist()[:20]
+    assert 1.0 - bad.mean() >= min_frac, idx.tolist()[:20]
 
 
 def test_plicp_degenerate_distances(engine):
@@ -190,9 +196,10 @@ def test_plicp_independent_of_cta_shape(threads):
             os.environ["ZHSM_PLICP_T"] = old
     both = (res["valid"] == 1) & (g["plicp_valid"][:300] == 1)
     assert np.array_equal(res["valid"], g["plicp_valid"][:300])
-    assert (pose_close(res["x"], g["plicp_x"][:300]) | ~both).mean() >= 0.995
-    assert (res["iterations"] == g["plicp_iterations"][:300]).mean() >= 0.995
-    assert ((res["corr_hash"] == g["plicp_hash"][:300]) | ~both).mean() >= 0.995
+    # the CTA shape must not change a single record of these 300 pairs (the one known near-tie pair of this log is 1004)
+    bad = ~(pose_close(res["x"], g["plicp_x"][:300]) | ~both) | (res["iterations"] != g["plicp_iterations"][:300]) | \
+        ((res["corr_hash"] != g["plicp_hash"][:300]) & both)
+    assert not bad.any(), (threads, np.flatnonzero(bad).tolist())
 
 
 def test_plicp_long_scans_poor_guesses_match_oracle():
@@ -224,7 +231,7 @@ def test_plicp_long_scans_poor_guesses_match_oracle():
     res, _, _ = eng.plicp(scans, ri, si, first_guess=guess, want_corr=True)
     eng.close()
     o = po.zhcsm_fmatch_batch(scans, ri, si, lz.fi_min, lz.dfi, 10, 3000, first_guess=guess, nthreads=8)
-    _assert_same_as_oracle(res, o, min_frac=0.995)
+    _assert_same_as_oracle(res, o, max_bad=0)   # 384 jobs: measured identical on every one (the newest walk code)
     assert (res["valid"] == 1).mean() > 0.9
 
 
