@@ -51,3 +51,63 @@ def best_of_starts(records, starts):
     score = np.where(r["valid"] == 1, r["error"] / np.maximum(r["nvalid"], 1), np.inf)
     idx = np.argmin(score, 1)
     return r[np.arange(r.shape[0]), idx], idx
+
+
+class OverlappedGather:
+    """The record all-gather of step k on a SIDE stream while step k+1 computes ("on a side stream,
+    overlapped with the next batch's compute").  The caller keeps `depth` local record buffers and rotates them:
+
+        k = g.slot()              # buffer this step writes; the compute stream first waits until the gather that last
+                                  # read buffer k is done (an event, no host block)
+        ... kernels write local[k] on the current stream ...
+        g.submit(local[k])        # gather local[k] into out[k] on the side stream, behind an event of the current stream
+        ...
+        g.result(k)               # [total, 128] of every rank, in job order; the current stream waits for that gather
+
+    Equal blocks only (the benchmark's weak-scaling shape).  On CPU tensors (gloo tests) there are no streams: submit
+    gathers at once."""
+
+    def __init__(self, total, like, depth=2, group=None):
+        import torch
+        import torch.distributed as dist
+        self.group, self.depth, self.k = group, depth, -1
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.cuda = like.is_cuda
+        self.out = [torch.empty((total, RECORD_BYTES), dtype=like.dtype, device=like.device) if self.world > 1 else None
+                    for _ in range(depth)]
+        self.done = [None] * depth
+        self.side = torch.cuda.Stream(device=like.device) if (self.cuda and self.world > 1) else None
+
+    def slot(self):
+        import torch
+        self.k = (self.k + 1) % self.depth
+        if self.done[self.k] is not None:
+            torch.cuda.current_stream().wait_event(self.done[self.k])
+        return self.k
+
+    def submit(self, local):
+        import torch
+        import torch.distributed as dist
+        k = self.k
+        if self.world == 1:
+            self.out[k] = local
+            return k
+        assert local.shape[0] * self.world == self.out[k].shape[0] and local.shape[1] == RECORD_BYTES
+        if self.side is None:
+            dist.all_gather_into_tensor(self.out[k], local.contiguous(), group=self.group)
+            return k
+        ready = torch.cuda.Event()
+        ready.record()                      # the records of this step are complete at this point of the compute stream
+        with torch.cuda.stream(self.side):
+            self.side.wait_event(ready)
+            dist.all_gather_into_tensor(self.out[k], local, group=self.group)
+            ev = torch.cuda.Event()
+            ev.record(self.side)
+        self.done[k] = ev
+        return k
+
+    def result(self, k):
+        import torch
+        if self.side is not None and self.done[k] is not None:
+            torch.cuda.current_stream().wait_event(self.done[k])
+        return self.out[k]

@@ -378,6 +378,21 @@ def consensus(poses, good, set_off):
     return keep, fp, fi
 
 
+def synth_pairs(npairs, n, fi_min, dfi, max_range_cm, first_pair=0, dmax_xy_m=0.10, dmax_th_rad=0.0872664626,
+                noise_m=0.01, dropout=0.01, seed=20261104, nthreads=1):
+    """The HOST twin of the device workload generator (oracle/synth_oracle.c): SURVEY 8d's synthetic scan pairs without
+    loading the product library.  -> (scans float32 [2*npairs][n] cm, truth float64 [npairs][3])."""
+    scans = np.zeros((2 * npairs, n), np.float32)
+    truth = np.zeros((npairs, 3), np.float64)
+    L = lib()
+    L.orc_synth_pairs.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_int, C.c_float, C.c_float, C.c_int,
+                                  C.c_float, C.c_float, C.c_float, C.c_float, C.c_ulonglong, C.c_int]
+    L.orc_synth_pairs(scans.ctypes.data, truth.ctypes.data, int(first_pair), int(npairs), int(n), float(fi_min), float(dfi),
+                      int(max_range_cm), float(dmax_xy_m), float(dmax_th_rad), float(noise_m), float(dropout), int(seed),
+                      int(nthreads))
+    return scans, truth
+
+
 def cov_to_information(cov6, scale=1.0, const_diag=None):
     """matchNodePairICP's information = covariance.inverse() (Eigen 3x3 cofactor formula), or the constant override."""
     cov6 = np.ascontiguousarray(cov6, np.float64).reshape(-1, 6)

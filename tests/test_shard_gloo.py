@@ -45,7 +45,22 @@ def _worker(rank, world, port, total, ok):
         out = shard.all_gather_records(local, total)
         got = out.numpy().view(RESULT_DTYPE).reshape(-1)
         want = _records(0, total)
-        ok[rank] = int(np.array_equal(got.view(np.uint8), want.view(np.uint8)))
+        good = np.array_equal(got.view(np.uint8), want.view(np.uint8))
+        if total % world == 0:
+            # the overlapped (double-buffered) gather of bench.py: three steps through two slots, each step's records
+            # differ, every result must be that step's
+            g = shard.OverlappedGather(total, local, depth=2)
+            for step in range(3):
+                k = g.slot()
+                assert k == step % 2
+                loc = local.clone()
+                loc[:, 100] = step + 1          # a byte of the record's reserved area marks the step
+                g.submit(loc)
+                res = g.result(k).numpy()
+                w = want.view(np.uint8).reshape(-1, 128).copy()
+                w[:, 100] = step + 1
+                good = good and np.array_equal(res, w)
+        ok[rank] = int(good)
     finally:
         dist.destroy_process_group()
 
