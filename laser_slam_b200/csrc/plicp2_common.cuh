@@ -36,6 +36,7 @@ struct Ctl {
     int sel_below;      // radix select: keys whose top byte is below the guess
     int npend;          // walks on the list of unfinished walks (plicp2_search.cuh)
     int pend_next;      // next list entry to be taken by a warp
+    int steps_pend;     // walk steps of the walks that went through the list (finish_unfinished)
 };
 
 // byte offsets into the dynamic shared memory block

@@ -10,6 +10,14 @@
 
 namespace plicp2 {
 
+// Which instances carry the list of unfinished walks (plicp2_search.cuh: a walk that outlives its budgets is finished
+// warp-wide after the round's barrier).  PLICP_LIST_MIN_T: tuning builds.
+#ifndef PLICP_LIST_MIN_T
+#define PLICP_LIST_MIN_T 256
+#endif
+template <int T>
+constexpr bool kList = T >= PLICP_LIST_MIN_T;
+
 // Per-phase cycle counters of thread 0 (tuning builds only: -DPLICP_PHASE_TIMING; the counters then REPLACE
 // x/cov/error/goodness/quality in the result record, see tools/gpu_probe_phases.py).
 struct PhaseClock {
@@ -17,9 +25,13 @@ struct PhaseClock {
     long long last, acc[20];
     __device__ __forceinline__ void start() { for (int k = 0; k < 20; k++) acc[k] = 0; last = clock64(); }
     __device__ __forceinline__ void mark(int k) { const long long c = clock64(); acc[k] += c - last; last = c; }
+    // one call of the walk routine by this thread's warp: cycles inside it (slot 1); slot 17 = calls (low 8 bits) +
+    // the longest lane's step count summed (above); acc[18]'s record field is a float: steps summed over ALL lanes there
+    __device__ __forceinline__ void walk(long long cycles, int max_steps) { acc[1] += cycles; acc[17] += ((long long)max_steps << 8) + 1; }
 #else
     __device__ __forceinline__ void start() {}
     __device__ __forceinline__ void mark(int) {}
+    __device__ __forceinline__ void walk(long long, int) {}
 #endif
 };
 
@@ -27,6 +39,7 @@ struct PhaseClock {
 // (= what the sequential algorithm executes); verify rounds that had work
 struct WalkDiag {
     int walks, first, rounds;
+    int steps;  // walk steps this thread executed (probes of its walks: the budgets of tricks_one count them)
 };
 
 // pose of the current iteration + what make_ray needs
@@ -50,7 +63,7 @@ struct IterCtx {
 // (process_pending finishes it and writes cj1 / cj2 then)
 template <bool LIST>
 __device__ __forceinline__ bool search_ray(const Lay &l, const WalkCtx &w, const IterCtx &it,
-                                           const PendRef<LIST> &pr, int i STATS_PARAM) {
+                                           const PendRef<LIST> &pr, int i, int &steps, PhaseClock &pc STATS_PARAM) {
     const Ray ray = make_ray(sens_point(PL_SH(const float, l.sensr), it.cs2, i), it.x0, it.x1, it.cs, it.sn, it.min_theta, it.C1);
     int j2 = -1;
 #ifdef PLICP_WALK_STATS
@@ -65,11 +78,19 @@ __device__ __forceinline__ bool search_ray(const Lay &l, const WalkCtx &w, const
     g_stats[4] += trips > 32 ? fast : 0;
     g_stats[5] = trips > g_stats[5] ? trips : g_stats[5];
 #else
+#ifdef PLICP_PHASE_TIMING
+    const long long c0_ = clock64();
+#endif
     const int j1 = tricks_one<LIST>(w, ray, (int)PL_SH(const short, l.spec)[i], &j2, pr, i);
+#ifdef PLICP_PHASE_TIMING
+    pc.walk(clock64() - c0_, __reduce_max_sync(__activemask(), (unsigned)j2 >> 16));
+#endif
 #endif
     if constexpr (LIST) {
-        if (j1 == WALK_PENDING) return false;
+        if (j1 == WALK_PENDING) return false;  // its steps so far travel with the list entry
     }
+    steps += (int)((unsigned)j2 >> 16);
+    j2 = (int)(short)(j2 & 0xffff);
     PL_SH(short, l.cj1)[i] = (short)j1;
     PL_SH(short, l.cj2)[i] = (short)(j1 >= 0 ? j2 : -1);
     return true;
@@ -84,8 +105,8 @@ static __device__ __noinline__ int finish_unfinished(const Lay l, const WalkCtx 
 
 template <int T>
 __device__ __forceinline__ int process_pending(const Lay &l, const WalkCtx &w, const IterCtx &it,
-                                               const PendRef<(T >= 256)> &pr) {
-    if constexpr (T < 256) {
+                                               const PendRef<kList<T>> &pr) {
+    if constexpr (!kList<T>) {
         return 0;  // the list exists in the long-scan instances only
     } else {
         const int np = PL_SH(Ctl, l.ctl)->npend;
@@ -119,11 +140,13 @@ static __device__ __noinline__ int finish_unfinished(const Lay l, const WalkCtx 
         u.wx = ray.wx; u.wy = ray.wy; u.rho2 = ray.rho2; u.phi = ray.phi; u.start_cell = ray.start_cell;
         double cb = bl.x;
         int cj = j1;
-        if (dir == 2) walk_warp_both(w, u, up, down, bl.y, last_down, &cb, &cj);
-        else walk_warp_one(w, u, up, dir, &cb, &cj);
+        int nwin;
+        if (dir == 2) nwin = walk_warp_both(w, u, up, down, bl.y, last_down, &cb, &cj);
+        else nwin = walk_warp_one(w, u, up, dir, &cb, &cj);
         int j2 = -1;
         const int r1 = walk_finish(w, ray.wx, ray.wy, cj, cb, &j2);
         if (lane == 0) {
+            atomicAdd(&ctl->steps_pend, pad + 32 * nwin);  // the lane's steps before the hand-over + 32 evaluations per window
             short *cj1 = PL_SH(short, l.cj1);
             changed |= (int)cj1[i] != r1;
             cj1[i] = (short)r1;
@@ -147,7 +170,7 @@ static __device__ __noinline__ int finish_unfinished(const Lay l, const WalkCtx 
 template <int T>
 __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const WalkCtx &w, const IterCtx &it, int C,
                                                          unsigned sens, bool chunked, const uint2 *jt_src,
-                                                         const PendRef<(T >= 256)> &pr, WalkDiag &dg,
+                                                         const PendRef<kList<T>> &pr, WalkDiag &dg,
                                                          PhaseClock &pc STATS_PARAM) {
     constexpr int NW = T / 32;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
@@ -168,7 +191,7 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
             if (sens >> k & 1u) {
                 dg.walks++;
                 dg.first++;
-                search_ray<(T >= 256)>(l, w, it, pr, k * T + t STATS_ARG);
+                search_ray<kList<T>>(l, w, it, pr, k * T + t, dg.steps, pc STATS_ARG);
             }
     } else {
         // thread t walks the rays [t*C, (t+1)*C) in order and hands last_best from one to the next: only the first
@@ -186,7 +209,7 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
             if (have) specw[i] = (short)lb;
             dg.walks++;
             dg.first++;
-            if (search_ray<(T >= 256)>(l, w, it, pr, i STATS_ARG)) {
+            if (search_ray<kList<T>>(l, w, it, pr, i, dg.steps, pc STATS_ARG)) {
                 const int c1 = cj1r[i];
                 lb = c1 >= 0 ? c1 : (int)specw[i];
                 have = true;
@@ -250,12 +273,12 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
             const int i = (int)queue[e];
             const int before = cj1[i];
             dg.walks++;
-            if (search_ray<(T >= 256)>(l, w, it, pr, i STATS_ARG)) changed |= (int)cj1[i] != before;
+            if (search_ray<kList<T>>(l, w, it, pr, i, dg.steps, pc STATS_ARG)) changed |= (int)cj1[i] != before;
             else unfinished = 1;  // on the list: process_pending says whether its j1 changed
         }
         // the usual end: nothing changed and nothing is unfinished -- last_best of every ray is what it was walked with
         if (!__syncthreads_or(changed | unfinished)) break;
-        if constexpr (T >= 256) {
+        if constexpr (kList<T>) {
             changed |= process_pending<T>(l, w, it, pr);
             if (!__syncthreads_or(changed)) break;
         }
@@ -268,8 +291,11 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
     return valid;
 }
 
+#ifndef PLICP_MINB_192
+#define PLICP_MINB_192 4   // resident CTAs per SM the 192-thread instance is compiled for (80 registers); tuning builds: 3
+#endif
 template <int T>
-__global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 2 : 1)) plicp2_kernel(PlicpArgs a) {
+__global__ void __launch_bounds__(T, (T <= 192 ? PLICP_MINB_192 : T <= 288 ? 2 : 1)) plicp2_kernel(PlicpArgs a) {
     constexpr int NW = T / 32;
     const int n = a.L.n;
     const int C = (n + T - 1) / T;
@@ -334,6 +360,7 @@ __global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 2 : 1)) plicp2_k
         ctl->topbyte = 0x3f;
         ctl->npend = 0;
         ctl->pend_next = 0;
+        ctl->steps_pend = 0;
         for (int k = 0; k < 3; k++) ctl->x[0][k] = a.first_guess ? a.first_guess[3 * (size_t)job + k] : 0.0;
         ctl->cs[0] = cos(ctl->x[0][2]);
         ctl->sn[0] = sin(ctl->x[0][2]);
@@ -369,8 +396,9 @@ __global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 2 : 1)) plicp2_k
         wc.refp = sb + l.refp; wc.rr2 = sb + l.rr2; wc.jt = sb + l.jt;
     }
     wc.n = n; wc.fi_min = L.fi_min; wc.dfi = L.dfi;
-    PendRef<(T >= 256)> pr;
-    if constexpr (T >= 256) {
+    wc.kq = walk_kq(L.dfi);
+    PendRef<kList<T>> pr;
+    if constexpr (kList<T>) {
         // the list of unfinished walks lies in the d2j area above the search's queue and group table
         const unsigned sb = (unsigned)__cvta_generic_to_shared(smem_raw);
         const unsigned lo = (sb + l.d2j + 2u * (unsigned)(n + C * NW) + 15u) & ~15u, hi = sb + l.d2j + 8u * (unsigned)n;
@@ -388,12 +416,14 @@ __global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 2 : 1)) plicp2_k
     double best_x[3] = {0, 0, 0}, x_first[3] = {0, 0, 0}, best_error = 0;
     int iterations = 0, nvalid0 = 0, n_loops = 0, restarted = 0, valid_out = 0, status = ZHSM_JOB_OK;
     unsigned valid = 0;
-    WalkDiag dg = {0, 0, 0};
+    WalkDiag dg = {0, 0, 0, 0};
 #ifdef PLICP_WALK_STATS
     int st_arr[6] = {0, 0, 0, 0, 0, 0};
     int *st_ = st_arr;
 #endif
 
+    // (the compiler unrolls this loop of 7: 600 KB of code, and 3.4 % FASTER on the 1080-beam batch than with
+    // `#pragma unroll 1` -- the first copy, the only one most jobs run, is specialised for loop == 0; measured r02p)
     for (int loop = 0; loop < 7; loop++) {
         int iteration = 0, all_ok = 1, par = 0, newest = 0;
         for (iteration = 0; iteration < max_it; iteration++) {
@@ -681,6 +711,7 @@ __global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 2 : 1)) plicp2_k
     const int walks_all = block_sum<T>(dg.walks, ctl->ired, 0);
 
     const int walks_first = block_sum<T>(dg.first, ctl->ired, 1);
+    const int steps_all = block_sum<T>(dg.steps, ctl->ired, 2) + ctl->steps_pend;
 #ifdef PLICP_WALK_STATS
     int sts[5];
     for (int k = 0; k < 5; k++) sts[k] = block_sum<T>(st_arr[k], ctl->ired, k & 3), __syncthreads();
@@ -702,6 +733,7 @@ __global__ void __launch_bounds__(T, (T <= 192 ? 4 : T <= 288 ? 2 : 1)) plicp2_k
         r.reserved[0] = walks_all;    // diagnostics: ray walks executed (speculation + re-searches)
         r.reserved[1] = walks_first;    // ... of which first-pass walks (= what the sequential algorithm does)
         r.reserved[2] = dg.rounds;      // verify rounds that had rays to re-search (summed over iterations)
+        r.reserved[3] = steps_all;      // walk steps executed: distance evaluations of all walks (bench.py: roofline.executed)
         if (valid_out) {
             r.x[0] = best_x[0];
             r.x[1] = best_x[1];

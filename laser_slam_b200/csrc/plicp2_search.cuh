@@ -54,7 +54,17 @@ struct WalkCtx {
     int n;
     float fi_min, dfi;
     double maxd2;
+    int kq;  // a probe fewer than kq rays beyond the start cell has dtheta < pi/2 for certain (walk_kq)
 };
+
+// CSM's stop test switches form where dtheta = |theta[j] - phi| exceeds pi/2.  With start_cell = (int)((phi - theta_0) *
+// n / (theta_{n-1} - theta_0)) exact (make_ray) and theta[j] = theta_0 + dfi * j, a probe `rel` rays beyond the start
+// cell in its walking direction has dtheta <= dfi * (rel + 2) * (1 + 1e-6): below kq = pi/2 / dfi - 4 the switch cannot
+// fire and the float angle arithmetic is skipped; at or above it the exact float test decides, as before.
+__host__ __device__ inline int walk_kq(float dfi) {
+    const float k = 1.5707963f / dfi - 4.f;
+    return k > 0.f ? (k < 1e6f ? (int)k : 1000000) : 0;
+}
 
 // The tables are constant while the walks run: plain (non-volatile) asm lets the compiler schedule the loads freely,
 // and the 32-bit shared addresses keep the address arithmetic out of the 64-bit generic path.
@@ -74,6 +84,17 @@ __device__ __forceinline__ int lds_b32(unsigned a) {
     int v;
     asm("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(a));
     return v;
+}
+// The three loads of a probe: squared reading, point, the direction's jump pair.  ptxas sinks a load behind any branch
+// whose body alone uses it -- in the r01 build the point's load sat behind the validity branch on the reading, two
+// shared-memory latencies in a row per probe (cuobjdump) -- so the callers' validity test reads the point as well
+// (an invalid ref ray's point is NaN), and the three loads issue back to back.
+__device__ __forceinline__ void lds_probe(unsigned a_rr2, unsigned a_q, unsigned a_hops, double &rr2, double2 &q, int &hops) {
+    asm("ld.shared.f64 %0, [%4];\n\t"
+        "ld.shared.v2.f64 {%1, %2}, [%5];\n\t"
+        "ld.shared.b32 %3, [%6];"
+        : "=d"(rr2), "=d"(q.x), "=d"(q.y), "=r"(hops)
+        : "r"(a_rr2), "r"(a_q), "r"(a_hops));
 }
 
 #ifdef PLICP_WALK_STATS
@@ -128,7 +149,7 @@ struct WalkState {
     int j1;
     int up, down;  // next index to probe in each direction (dir = +-1: `up` holds the one index)
     int dir;       // +1 / -1: one direction left; 2: both directions alive
-    int pad_;
+    int pad_;      // steps the walk had executed when it was handed over
 };
 static_assert(sizeof(WalkState) == 48, "WalkState is a 48-byte shared-memory record");
 
@@ -151,7 +172,7 @@ __device__ __forceinline__ bool pend_push(const PendRef<true> &c, const WalkStat
     asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(a), "d"(st.best), "d"(st.last_up) : "memory");
     asm volatile("st.shared.f64 [%0], %1;" ::"r"(a + 16u), "d"(st.last_down) : "memory");
     asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(a + 24u), "r"(st.i), "r"(st.j1) : "memory");
-    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a + 32u), "r"(st.up), "r"(st.down), "r"(st.dir), "r"(0) : "memory");
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a + 32u), "r"(st.up), "r"(st.down), "r"(st.dir), "r"(st.pad_) : "memory");
     return true;
 }
 
@@ -180,6 +201,7 @@ static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int 
     int trips = 0;
 #endif
     const float fi_min = c.fi_min, dfi = c.dfi, phi = r.phi;
+    const int kq = c.kq;
     // The general loop: the next probe goes where the last distance was smaller (or where the walk is still alive).
     // A walk that is still running after WALK_BUDGET probes with one direction ended leaves for the loop below.
     int budget = WALK_BUDGET;
@@ -195,6 +217,7 @@ static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int 
                 WalkState st;
                 st.best = best; st.last_up = last_up; st.last_down = last_down;
                 st.i = ray_i; st.j1 = j1; st.up = up; st.down = down; st.dir = 2;
+                st.pad_ = WALK_BUDGET - budget;
                 if (pend_push(pr, st)) {
 #ifdef PLICP_WALK_STATS
                     g_walk_trips = trips;
@@ -211,33 +234,30 @@ static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int 
             stopped |= bit;
             continue;
         }
-        const double rr2 = lds_f64(a_rr2 + 8u * idx);
-        const double2 q = lds_f64x2(a_refp + 16u * idx);
-        const int hops = lds_b32((now_up ? a_jt_up : a_jt_dn) + 4u * idx);  // both jumps of this direction
+        double rr2;
+        double2 q;
+        int hops;  // both jumps of this direction
+        lds_probe(a_rr2 + 8u * idx, a_refp + 16u * idx, (now_up ? a_jt_up : a_jt_dn) + 4u * idx, rr2, q, hops);
         const int sdir = now_up ? 1 : -1;
         int nidx = idx + sdir;
-        if (rr2 >= 0) {
+        // an invalid ref ray has rr2 = -1 AND a NaN point: testing both makes the branch need the point, which keeps
+        // ptxas from sinking the point's load behind this branch (the second of two latencies in a row)
+        if ((rr2 >= 0) & (q.x == q.x)) {
             const double d = dist2(wx, wy, q.x, q.y);
             last_up = now_up ? d : last_up;
             last_down = now_up ? last_down : d;
             const bool better = d < best;
             j1 = better ? idx : j1;
             best = better ? d : best;
-            if ((idx - start_cell) * sdir > 0) {  // beyond the start cell in the walking direction
-                const float dth = theta_f(fi_min, dfi, idx) - phi;  // phi - theta is the exact negation
-                const float sdth = now_up ? dth : -dth;
+            const int rel = (idx - start_cell) * sdir;
+            if (rel > 0) {  // beyond the start cell in the walking direction
                 const double cross = wx * q.y - wy * q.x;
-                // stop = dth > pi/2 ? rho2 > best : cross^2 > best * rr2, kept in predicate registers
-                int stop;
-                asm("{ .reg .pred pf, pa, pb;\n\t"
-                    "setp.gt.f32 pf, %1, %2;\n\t"
-                    "setp.gt.and.f64 pa, %3, %4, pf;\n\t"
-                    "not.pred pf, pf;\n\t"
-                    "setp.gt.and.f64 pb, %5, %6, pf;\n\t"
-                    "or.pred pa, pa, pb;\n\t"
-                    "selp.s32 %0, 1, 0, pa; }"
-                    : "=r"(stop)
-                    : "f"(sdth), "f"(HALF_PI_F), "d"(rho2), "d"(best), "d"(cross * cross), "d"(best * rr2));
+                // stop = dth > pi/2 ? rho2 > best : cross^2 > best * rr2
+                bool stop = cross * cross > best * rr2;
+                if (rel >= kq) {  // only here can dth exceed pi/2 (walk_kq): the exact float test, as the reference orders it
+                    const float dth = theta_f(fi_min, dfi, idx) - phi;  // phi - theta is the exact negation
+                    if ((now_up ? dth : -dth) > HALF_PI_F) stop = rho2 > best;
+                }
                 if (stop) { stopped |= bit; continue; }
                 nidx = idx + (rr2 < rho2 ? (int)(short)hops : hops >> 16);
             }
@@ -251,18 +271,20 @@ static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int 
     // last distances).  The rare walks that cross most of the scan (about 1 in 600, 100+ probes) spend nearly all
     // their probes here with one lane of the warp alive, and a whole search phase waits for them: instructions per
     // probe are what counts.  Short walks never come here, so the warp does not serialise the two loops.
+    int solo = SOLO_BUDGET;
     if (stopped != 3) {
         const bool go_up = stopped == 2;
         const int sdir = go_up ? 1 : -1;
         const unsigned a_jt = go_up ? a_jt_up : a_jt_dn;
         int idx = go_up ? up : down;
-        int solo = SOLO_BUDGET;
 #pragma unroll 1
         while ((unsigned)idx <= (unsigned)to) {
-            if (LIST && --solo < 0 && ask) {
+            --solo;  // (counted in every instance: the walk's step count, see the return value)
+            if (LIST && solo < 0 && ask) {
                 WalkState st;
                 st.best = best; st.last_up = 0; st.last_down = 0;
                 st.i = ray_i; st.j1 = j1; st.up = idx; st.down = 0; st.dir = sdir;
+                st.pad_ = (WALK_BUDGET - budget) + (SOLO_BUDGET - solo);
                 if (pend_push(pr, st)) {
 #ifdef PLICP_WALK_STATS
                     g_walk_trips = trips;
@@ -274,25 +296,26 @@ static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int 
 #ifdef PLICP_WALK_STATS
             trips += 0x10001;
 #endif
-            const double rr2 = lds_f64(a_rr2 + 8u * idx);
-            const double2 q = lds_f64x2(a_refp + 16u * idx);
-            const int hops = lds_b32(a_jt + 4u * idx);
+            double rr2;
+            double2 q;
+            int hops;
+            lds_probe(a_rr2 + 8u * idx, a_refp + 16u * idx, a_jt + 4u * idx, rr2, q, hops);
             int hop = hops >> 16;  // an invalid ref ray: the skip over its whole run
-            if (rr2 >= 0) {
+            if ((rr2 >= 0) & (q.x == q.x)) {
                 const double d = dist2(wx, wy, q.x, q.y);
                 const bool better = d < best;
                 j1 = better ? idx : j1;
                 best = better ? d : best;
                 hop = sdir;
-                if ((idx - start_cell) * sdir > 0) {
-                    const float dth = theta_f(fi_min, dfi, idx) - phi;
-                    const float sdth = go_up ? dth : -dth;
-                    if (sdth > HALF_PI_F) {
-                        if (rho2 > best) break;
-                    } else {
-                        const double cross = wx * q.y - wy * q.x;
-                        if (cross * cross > best * rr2) break;
+                const int rel = (idx - start_cell) * sdir;
+                if (rel > 0) {
+                    const double cross = wx * q.y - wy * q.x;
+                    bool stop = cross * cross > best * rr2;
+                    if (rel >= kq) {
+                        const float dth = theta_f(fi_min, dfi, idx) - phi;
+                        if ((go_up ? dth : -dth) > HALF_PI_F) stop = rho2 > best;
                     }
+                    if (stop) break;
                     hop = rr2 < rho2 ? (int)(short)hops : (hops >> 16);
                 }
             }
@@ -302,7 +325,10 @@ static __device__ __noinline__ int tricks_one(const WalkCtx c, const Ray r, int 
 #ifdef PLICP_WALK_STATS
     g_walk_trips = trips;
 #endif
-    return walk_finish(c, wx, wy, j1, best, j2out);
+    // *j2out: j2 in the low half, the walk's executed steps (trips of the two loops: the budgets count them) above
+    const int r1 = walk_finish(c, wx, wy, j1, best, j2out);
+    *j2out = (*j2out & 0xffff) | (((WALK_BUDGET - budget) + (SOLO_BUDGET - solo)) << 16);
+    return r1;
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -416,12 +442,13 @@ __device__ __forceinline__ void win_take(const Win &w, int lane, int from, int l
 }
 
 // One direction alone, from idx, until it stops or leaves the scan.
-__device__ __forceinline__ void chain_one(const WalkCtx &c, const RayU &u, int idx, int sdir, double &cb, int &cj) {
+__device__ __forceinline__ void chain_one(const WalkCtx &c, const RayU &u, int idx, int sdir, double &cb, int &cj, int &nwin) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const int to = c.n - 1;
 #pragma unroll 1
     while ((unsigned)idx <= (unsigned)to) {
+        nwin++;
         const Win w = load_window(c, u, idx, sdir, cb);
         const unsigned ends = __ballot_sync(FULL, win_stop(w, u, lane, cb)) | w.oobm;
         const int last = ends ? __ffs(ends) - 1 : 31;
@@ -432,12 +459,14 @@ __device__ __forceinline__ void chain_one(const WalkCtx &c, const RayU &u, int i
 }
 
 // All arguments warp-uniform (a list entry and its ray); the result comes back in (cb, cj).
-static __device__ __noinline__ void walk_warp_one(const WalkCtx c, const RayU u, int idx, int sdir, double *cbp, int *cjp) {
+static __device__ __noinline__ int walk_warp_one(const WalkCtx c, const RayU u, int idx, int sdir, double *cbp, int *cjp) {
     double cb = *cbp;
     int cj = *cjp;
-    chain_one(c, u, idx, sdir, cb, cj);
+    int nwin = 0;
+    chain_one(c, u, idx, sdir, cb, cj, nwin);
     *cbp = cb;
     *cjp = cj;
+    return nwin;  // windows of 32 rays loaded (every lane evaluates its ray's distance)
 }
 
 // Both directions alive.  The sequential loop probes upwards while last_up < last_down and downwards otherwise, so
@@ -446,8 +475,8 @@ static __device__ __noinline__ void walk_warp_one(const WalkCtx c, const RayU u,
 // stop tests inside it see min(best before the run, prefix minimum), and the first of {run end, stop, end of the
 // scan} decides how it goes on: with the other direction, with the other direction alone (chain_one), or with the
 // next window of the same direction.
-static __device__ __noinline__ void walk_warp_both(const WalkCtx c, const RayU u, int up, int down, double last_up,
-                                                   double last_down, double *cbp, int *cjp) {
+static __device__ __noinline__ int walk_warp_both(const WalkCtx c, const RayU u, int up, int down, double last_up,
+                                                  double last_down, double *cbp, int *cjp) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     double cb = *cbp;
@@ -458,6 +487,7 @@ static __device__ __noinline__ void walk_warp_both(const WalkCtx c, const RayU u
     Win W[2];
     int pos[2] = {32, 32};  // next lane to take in each window; 32: the window has to be loaded (from nextidx)
     int alone = -1;         // the direction that goes on alone once the other has ended
+    int nwin = 0;
 #pragma unroll 1
     for (;;) {
         const int s = last[1] < last[0] ? 1 : 0;  // 1: upwards
@@ -466,6 +496,7 @@ static __device__ __noinline__ void walk_warp_both(const WalkCtx c, const RayU u
             if ((unsigned)nextidx[s] > (unsigned)to) { alone = s ^ 1; break; }  // ran off the scan: this side has ended
             if (s) W[1] = load_window(c, u, nextidx[1], +1, cb); else W[0] = load_window(c, u, nextidx[0], -1, cb);
             pos[s] = 0;
+            nwin++;
         }
         const Win &w = s ? W[1] : W[0];
         const int from = pos[s];
@@ -506,10 +537,11 @@ static __device__ __noinline__ void walk_warp_both(const WalkCtx c, const RayU u
     // one direction is left: from where it stands, alone
     {
         const int idx = pos[alone] < 32 ? __shfl_sync(FULL, (alone ? W[1].my : W[0].my), pos[alone]) : nextidx[alone];
-        chain_one(c, u, idx, alone ? 1 : -1, cb, cj);
+        chain_one(c, u, idx, alone ? 1 : -1, cb, cj, nwin);
     }
     *cbp = cb;
     *cjp = cj;
+    return nwin;
 }
 
 }  // namespace plicp2

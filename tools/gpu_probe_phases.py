@@ -32,3 +32,8 @@ print(f"kernel {eng.last_kernel_ms():.2f} ms for {P} pairs; iterations/pair {r['
       f"cycles/job {tot.mean():.0f} (thread 0 clock64, includes barrier waits and time-slicing with co-resident CTAs)")
 for k, nm in enumerate(names):
     print(f"  {nm:22s} {ph[:, k].mean():10.0f} cycles/job  {100 * ph[:, k].sum() / tot.sum():5.1f} %   per iteration {ph[:, k].sum() / r['iterations'].sum():8.0f}")
+w_cyc, w_pack = ph[:, 1], ph[:, 17]
+calls = np.mod(w_pack, 256.0); msteps = np.floor(w_pack / 256.0)
+print(f"walk routine (thread 0's warp): {calls.mean():.0f} calls/job, {w_cyc.sum() / calls.sum():.0f} cycles per call, "
+      f"longest lane {msteps.sum() / calls.sum():.1f} steps per call -> {w_cyc.sum() / msteps.sum():.0f} cycles per step of the longest lane; "
+      f"inside the routine: {100 * w_cyc.sum() / (ph[:, 2].sum() + ph[:, 3].sum()):.0f} % of the two search phases")
