@@ -20,6 +20,7 @@ namespace plicp2 {
 constexpr int NSUM = 16;  // 14 GPC sums + total_error + pad
 
 struct Ctl {
+    unsigned long long mbar;  // mbarrier of the bulk (TMA) copy that brings the jump tables back (PLICP_TMA_JT builds)
     double x[2][3];     // pose ping-pong: x[p] is x_old of the iteration with parity p, x[p^1] receives x_new
     double cs[2], sn[2];  // cos/sin of x[p][2]
     double error;       // total_error of the last iteration
@@ -87,6 +88,30 @@ __host__ __device__ inline size_t smem_bytes(int n, int nthreads) { return make_
 
 extern __shared__ __align__(16) unsigned char smem_raw[];
 #define PL_SH(type, off) (reinterpret_cast<type *>(smem_raw + (off)))
+
+// ---- 1-D bulk copy global -> shared through the TMA unit, completion on an mbarrier (sm_90+: cp.async.bulk) ----------
+// One thread arms the barrier with the byte count and issues the copy; every thread that needs the data waits for the
+// barrier's phase.  src, dst and bytes must be multiples of 16.
+__device__ __forceinline__ void mbar_init(unsigned mbar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mbar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void bulk_load_1d(unsigned dst, const void *src, unsigned bytes, unsigned mbar) {
+    // shared memory written before by ordinary stores / atomics: order those against the async proxy's writes
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(mbar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned mbar, unsigned phase) {
+    asm volatile("{\n\t"
+                 ".reg .pred p;\n\t"
+                 "MBAR_WAIT:\n\t"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+                 "@p bra MBAR_DONE;\n\t"
+                 "bra MBAR_WAIT;\n\t"
+                 "MBAR_DONE:\n\t"
+                 "}" ::"r"(mbar), "r"(phase) : "memory");
+}
 
 // theta[j] exactly as fromPMScan2LDP builds it (src/zhcsm/ZHCanonical_Matcher.cpp:210): float fi_min + float dfi*j
 __device__ __forceinline__ float theta_f(float fi_min, float dfi, int j) {

@@ -158,6 +158,30 @@ static __device__ __noinline__ int finish_unfinished(const Lay l, const WalkCtx 
     return changed;
 }
 
+// The jump tables' way back into shared memory as ONE bulk copy (cp.async.bulk through the TMA unit, completion on an
+// mbarrier) issued by thread 0 as soon as the radix select is done with the area they share -- the copy then runs behind
+// the sums, the hash and the solve of the same iteration, and the next search only waits for the barrier's phase.
+// PLICP_TMA_JT builds; off, the threads copy the tables themselves at the start of every search.  Needs 16-byte
+// aligned tables: an even beam count.  All members are uniform over the CTA.
+struct JtPrefetch {
+    bool on;            // this job uses the bulk copy
+    bool pending;       // a copy has been issued and not yet waited for
+    unsigned phase;     // parity of the barrier phase the next wait observes
+    unsigned mbar, dst, bytes;
+    const void *src;
+    __device__ __forceinline__ void issue() {  // call by every thread, after a barrier that ends all uses of the area
+        if (!on) return;
+        if (threadIdx.x == 0) bulk_load_1d(dst, src, bytes, mbar);
+        pending = true;
+    }
+    __device__ __forceinline__ void wait() {
+        if (!on || !pending) return;
+        mbar_wait(mbar, phase);
+        phase ^= 1u;
+        pending = false;
+    }
+};
+
 // find_correspondences_tricks for the whole scan: speculate / verify / re-search until the sequential result.
 // First pass: thread t walks its rays k*T+t with the last_best the previous iteration saw (spec[]).
 // Verify: last_best before ray i is j1 of the nearest earlier ray holding a correspondence -- found with warp ballots
@@ -171,7 +195,7 @@ template <int T>
 __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const WalkCtx &w, const IterCtx &it, int C,
                                                          unsigned sens, bool chunked, const uint2 *jt_src,
                                                          const PendRef<kList<T>> &pr, WalkDiag &dg,
-                                                         PhaseClock &pc STATS_PARAM) {
+                                                         PhaseClock &pc, JtPrefetch &tma STATS_PARAM) {
     constexpr int NW = T / 32;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int n = w.n;
@@ -181,9 +205,14 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
     if (jt_src) {
         // the radix select's histograms share the jump tables' shared memory (Lay::jt_shared): bring the tables back
         // (8 bytes per ray from this job's scratch, L2-resident)
-        uint2 *dst = PL_SH(uint2, l.jt);
-        for (int q = t; q < n; q += T) dst[q] = __ldcs(jt_src + q);  // streaming: leave the L1 to the cs table
-        __syncthreads();
+        if (tma.on) {
+            // ... which a bulk copy issued after the previous select has already done (JtPrefetch): wait for its phase
+            tma.wait();
+        } else {
+            uint2 *dst = PL_SH(uint2, l.jt);
+            for (int q = t; q < n; q += T) dst[q] = __ldcs(jt_src + q);  // streaming: leave the L1 to the cs table
+            __syncthreads();
+        }
     }
     if (!chunked) {
 #pragma unroll 1
@@ -338,6 +367,21 @@ __global__ void __launch_bounds__(T, (T <= 192 ? PLICP_MINB_192 : T <= 288 ? 2 :
         for (int q = t; q < n; q += T) dst[q] = __ldcs(jt_job + q);
     }
     const uint2 *jt_src = l.jt_shared ? jt_job : nullptr;  // find_correspondences copies them in before every search
+    JtPrefetch tma;
+    tma.on = false; tma.pending = false; tma.phase = 0;
+#ifdef PLICP_TMA_JT
+    if (jt_src && (n & 1) == 0) {
+        const unsigned sb = (unsigned)__cvta_generic_to_shared(smem_raw);
+        tma.on = true;
+        tma.mbar = sb + l.ctl + (unsigned)offsetof(Ctl, mbar);
+        tma.dst = sb + l.jt;
+        tma.bytes = 8u * (unsigned)n;
+        tma.src = jt_job;
+        if (t == 0) mbar_init(tma.mbar, 1);
+        __syncthreads();   // the barrier object is initialised before anyone arms or polls it
+        tma.issue();       // the first search's tables travel while the scans are loaded and converted
+    }
+#endif
 #pragma unroll 1
     for (int k = 0; k < C; k++) {
         const int i = k * T + t;
@@ -382,6 +426,7 @@ __global__ void __launch_bounds__(T, (T <= 192 ? PLICP_MINB_192 : T <= 288 ? 2 :
             *res = r;
         }
         if (oj1) for (int i = t; i < n; i += T) { oj1[i] = -1; oj2[i] = -1; }
+        tma.wait();  // nothing may be in flight into this CTA's shared memory when it exits
         return;
     }
     pc.mark(0);  // the block sums above were barriers: the tables are in place
@@ -432,7 +477,7 @@ __global__ void __launch_bounds__(T, (T <= 192 ? PLICP_MINB_192 : T <= 288 ? 2 :
             it.cs = ctl->cs[par];
             it.sn = ctl->sn[par];
             if (t == 0) ctl->hash_acc[iteration & 1] = 0;
-            valid = find_correspondences<T>(l, wc, it, C, sens, iteration < a.chunk_iters, jt_src, pr, dg, pc STATS_ARG);
+            valid = find_correspondences<T>(l, wc, it, C, sens, iteration < a.chunk_iters, jt_src, pr, dg, pc, tma STATS_ARG);
             if (P.outliers_remove_doubles) {
                 for (int j = t; j < n; j += T) d2j[j] = BIG;  // the search used this area as its queue
                 __syncthreads();
@@ -571,6 +616,7 @@ __global__ void __launch_bounds__(T, (T <= 192 ? PLICP_MINB_192 : T <= 288 ? 2 :
                 for (int q = 0; q < NSUM - 1; q++) red[warp * NSUM + q] = S[q];
             }
             const int num_after = block_sum<T>(nkept, ctl->ired, 3);  // barrier: publishes red, cj1, cj2
+            tma.issue();  // every thread is past the select: the histograms' area is free for the next search's tables
             pc.mark(6);
             // ld_corr_hash of this iteration's correspondences, in parallel
             {
@@ -690,8 +736,9 @@ __global__ void __launch_bounds__(T, (T <= 192 ? PLICP_MINB_192 : T <= 288 ? 2 :
         it.cs = ctl->cs[0];
         it.sn = ctl->sn[0];
         // "recompute correspondences in case of restarts" (icp.c): world coords at best x + tricks, no outlier pass
-        if (v_restarted) valid = find_correspondences<T>(l, wc, it, C, sens, a.chunk_iters > 0, jt_src, pr, dg, pc STATS_ARG);
+        if (v_restarted) valid = find_correspondences<T>(l, wc, it, C, sens, a.chunk_iters > 0, jt_src, pr, dg, pc, tma STATS_ARG);
     }
+    tma.wait();  // a prefetch issued by the last iteration must have landed before the CTA gives up its shared memory
     if (t == 0) ctl->hash_acc[0] = 0;
 #pragma unroll 1
     for (int k = 0; k < C; k++) {
