@@ -294,6 +294,28 @@ long long zhsm_frame_unpack(const uint8_t *buf, long long len, unsigned flags, z
 zhsm_status zhsm_submap_cloud(zhsm_handle *h, const float *scans, const double *traj, int K, float *out_x, float *out_y,
                               int cap, int *count, int *dims);
 
+/* ---- several GPUs of one box from ONE process ---------------------------------------------------------
+ * The reference has no multi-GPU code; north_star: batches "sharded across the 8 GPUs of one box, with NCCL over NVLink
+ * used only to all-gather result poses and covariances for the pose graph", host side C++.  A group = one handle per
+ * device + an NCCL communicator over them (ncclCommInitAll; libnccl.so.2 is loaded with dlopen here, libzhsm.so itself
+ * does not depend on it).  zhsm_group_plicp_batch is zhsm_plicp_batch with HOST arrays: the B jobs are cut into
+ * contiguous blocks of ceil(B / n) (GPU k owns jobs [k * block, (k+1) * block)), each GPU receives only the slice of the
+ * scan pool its block references, all GPUs match at once, and ONE ncclAllGather of the 128-byte records leaves every
+ * record on every GPU (zhsm_group_gathered: device memory of GPU k, [n * block] records, the first B in job order,
+ * valid until the next group call) and in results[B] on the host.  flags: 0 or ZHSM_FILTER_SCANS.  One caller thread per
+ * group.  The torchrun path (bench.py, one process per GPU) uses the same partition and the same gather. */
+typedef struct zhsm_group zhsm_group;
+zhsm_status zhsm_group_create(const int *devices, int n, zhsm_group **out);
+void zhsm_group_destroy(zhsm_group *g);
+int zhsm_group_size(zhsm_group *g);
+zhsm_handle *zhsm_group_handle(zhsm_group *g, int k);
+const char *zhsm_group_last_error(zhsm_group *g);
+zhsm_status zhsm_group_set_laser(zhsm_group *g, const zhsm_laser *laser);
+zhsm_status zhsm_group_plicp_batch(zhsm_group *g, const float *scans, int S, const int32_t *ref_idx,
+                                   const int32_t *sens_idx, const double *first_guess, int B,
+                                   const zhsm_plicp_params *params, zhsm_result *results, unsigned flags);
+const zhsm_result *zhsm_group_gathered(zhsm_group *g, int k, int *block, int *B);
+
 /* blocks until everything queued on the handle's stream (or the given one) is done */
 zhsm_status zhsm_sync(zhsm_handle *h, void *cuda_stream);
 

@@ -145,6 +145,18 @@ def load_library():
     L.zhsm_frame_pack.restype = C.c_longlong
     L.zhsm_frame_unpack.argtypes = [vp, C.c_longlong, u32, C.POINTER(Frame), vp, i32]
     L.zhsm_frame_unpack.restype = C.c_longlong
+    L.zhsm_group_create.argtypes = [vp, i32, C.POINTER(vp)]
+    L.zhsm_group_destroy.argtypes = [vp]
+    L.zhsm_group_destroy.restype = None
+    L.zhsm_group_size.argtypes = [vp]
+    L.zhsm_group_handle.argtypes = [vp, i32]
+    L.zhsm_group_handle.restype = vp
+    L.zhsm_group_last_error.argtypes = [vp]
+    L.zhsm_group_last_error.restype = C.c_char_p
+    L.zhsm_group_set_laser.argtypes = [vp, C.POINTER(Laser)]
+    L.zhsm_group_plicp_batch.argtypes = [vp, vp, i32, vp, vp, vp, i32, C.POINTER(PlicpParams), vp, u32]
+    L.zhsm_group_gathered.argtypes = [vp, i32, C.POINTER(i32), C.POINTER(i32)]
+    L.zhsm_group_gathered.restype = vp
     L.zhsm_sync.argtypes = [vp, vp]
     L.zhsm_launch_count.argtypes = [vp]
     L.zhsm_launch_count.restype = C.c_uint64
@@ -538,3 +550,52 @@ class Engine:
 
     def last_kernel_ms(self):
         return float(self.L.zhsm_last_kernel_ms(self.h))
+
+
+class Group:
+    """zhsm_group_*: n GPUs of one box driven from this process (one handle per device + an NCCL communicator).
+    plicp() is Engine.plicp with host arrays, sharded by contiguous job blocks, the records all-gathered."""
+
+    def __init__(self, devices):
+        self.L = load_library()
+        devs = np.ascontiguousarray(devices, np.int32)
+        g = C.c_void_p()
+        st = self.L.zhsm_group_create(devs.ctypes.data, int(devs.size), C.byref(g))
+        if st != 0:
+            raise ZhsmError(f"zhsm_group_create({list(devices)}) failed with status {st}")
+        self.g, self.n, self.laser = g, int(devs.size), None
+
+    def close(self):
+        if getattr(self, "g", None):
+            self.L.zhsm_group_destroy(self.g)
+            self.g = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, st, what):
+        if st != 0:
+            raise ZhsmError(f"{what}: status {st}: {self.L.zhsm_group_last_error(self.g).decode()}")
+
+    def set_laser(self, laser):
+        self.laser = laser
+        self._check(self.L.zhsm_group_set_laser(self.g, C.byref(laser)), "zhsm_group_set_laser")
+
+    def plicp(self, scans, ref_idx, sens_idx, first_guess=None, params=None, filter_scans=False):
+        assert scans.dtype == np.float32 and scans.flags.c_contiguous and scans.shape[1] == self.laser.n
+        ri, si = np.ascontiguousarray(ref_idx, np.int32), np.ascontiguousarray(sens_idx, np.int32)
+        fg = None if first_guess is None else np.ascontiguousarray(first_guess, np.float64)
+        res = np.zeros(ri.size, RESULT_DTYPE)
+        self._check(self.L.zhsm_group_plicp_batch(self.g, _ptr(scans), int(scans.shape[0]), _ptr(ri), _ptr(si), _ptr(fg), int(ri.size),
+                                                  C.byref(params) if params is not None else None, _ptr(res),
+                                                  FILTER_SCANS if filter_scans else 0), "zhsm_group_plicp_batch")
+        return res
+
+    def gathered(self, k):
+        """(device pointer of GPU k's copy of all records, block, B) of the last batch."""
+        block, B = C.c_int(), C.c_int()
+        p = self.L.zhsm_group_gathered(self.g, int(k), C.byref(block), C.byref(B))
+        return p, block.value, B.value
