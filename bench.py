@@ -559,7 +559,7 @@ def measure_c5(zh, eng, dev, stream, world, rank, P, steps, warmup, args, peak64
         if record:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
-        eng.plicp(work, ri, si, first_guess=guess, results=res, stream=stream)
+        eng.plicp(work, ri, si, first_guess=guess, results=res, stream=stream, multistart=args.c5_multistart)
         if record:
             e1.record()
             kern_events.append((e0, e1))
@@ -595,7 +595,7 @@ def measure_c5(zh, eng, dev, stream, world, rank, P, steps, warmup, args, peak64
 
     def e2e_step():
         r_dev = torch.empty((P * G, 128), dtype=torch.uint8, device=dev)
-        eng.plicp(host_np, ri_h, si_h, first_guess=guess_h, results=r_dev, filter_scans=True, stream=stream)
+        eng.plicp(host_np, ri_h, si_h, first_guess=guess_h, results=r_dev, filter_scans=True, stream=stream, multistart=args.c5_multistart)
         _, rec = eng.best_of_starts(r_dev, P, G, criterion=E.BEST_MEAN_ERROR, stream=stream)
         if world > 1:
             rec = shard.all_gather_records(rec, world * P)
@@ -635,7 +635,7 @@ def measure_c5(zh, eng, dev, stream, world, rank, P, steps, warmup, args, peak64
                     "api": "zhsm_plicp_batch(host scans + jobs + first guesses, ZHSM_FILTER_SCANS) -> zhsm_best_of_starts -> best records to the host"},
             "gpu_launches": launches,
             "roofline": roofline_block(flops, {**fdet, "iterations_per_start": float(r["iterations"].mean())}, kern_ms, peak64,
-                                       "fp64_cuda_core", "plicp2_kernel<256> + jump_tables_kernel", ex),
+                                       "fp64_cuda_core", ("plicp2ms::plicp2_kernel<128> (4 starts of a pair per CTA)" if args.c5_multistart else "plicp2_kernel<256>") + " + jump_tables_kernel", ex),
             "results": {"valid_frac": float((r["valid"] == 1).mean()),
                         "pairs_with_best_start_within_2cm_0.5deg_of_truth": float(ok.mean())}}
     if world == 1 and not args.no_cpu:
@@ -878,6 +878,9 @@ def main():
     ap.add_argument("--cpu-pairs", type=int, default=100_000, help="cpu_baseline sample (pairs)")
     ap.add_argument("--ref-pairs", type=int, default=20_000, help="--impl reference: pairs per step")
     ap.add_argument("--c5-pairs", type=int, default=7812, help="config 5: pairs per GPU (62 500 / 8)")
+    ap.add_argument("--c5-multistart", action="store_true",
+                    help="config 5 through ZHSM_MULTISTART (four starts of a pair per CTA); measured SLOWER (68 k vs 90 k "
+                         "matches/s, DESIGN 9), so off")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-configs", action="store_true", help="skip the C1/C2/C3/C5 block of the default line")
     ap.add_argument("--workload", choices=["c4", "c5"], default="c4",

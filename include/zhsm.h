@@ -109,6 +109,14 @@ typedef struct zhsm_result {
  * With ZHSM_WRITEBACK_SCANS a host pool receives the filtered ranges back, like FMatch mutates lsa->r. */
 #define ZHSM_FILTER_SCANS 8u
 #define ZHSM_WRITEBACK_SCANS 16u
+/* zhsm_plicp_batch only, multi-start batches (loop-closure candidates with G first guesses per scan pair, the order
+ * zhsm_best_of_starts reads: pair-major): the caller promises that B is a multiple of 4 and that jobs 4k .. 4k+3 share
+ * both scan indices.  Long scans (> 1472 beams) are then matched four jobs per CTA over ONE staged copy of the two
+ * scans (twice the jobs per SM); shorter scans ignore the flag.  The same records either way: every integer field and
+ * every correspondence equal, poses equal to rounding (1e-12).  A job that breaks the promise is failed with
+ * ZHSM_JOB_INVALID_SCAN, never matched against the wrong scans.  MEASURED SLOWER than the default path on B200
+ * (68 k against 90 k matches/s at 2048 beams): leave it off unless your own measurement says otherwise. */
+#define ZHSM_MULTISTART 32u
 
 zhsm_status zhsm_create(int device, zhsm_handle **out);
 void zhsm_destroy(zhsm_handle *h);

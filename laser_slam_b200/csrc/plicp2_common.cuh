@@ -15,9 +15,45 @@
 
 #include "zhsm_internal.h"
 
-namespace plicp2 {
+// Jobs per CTA.  1 (every instance but one): a CTA owns one job.  4 (plicp2_ms128.cu, the multi-start instance): a CTA
+// owns four jobs ("slots") that share BOTH scans -- four first guesses of one scan pair -- as four groups of T threads
+// over ONE staged copy of the ref scan's points, squared readings and jump tables and of the sens readings; everything
+// else (correspondences, queues, histograms, sums, control block) is per slot, and the slots never wait for each
+// other after the load: every barrier of the job is a named barrier of its own group (pl_sync).  Each instance file is
+// its own namespace, so the single-job instances are untouched by the other's existence.
+#ifndef PLICP_NS
+#define PLICP_NS 1
+#endif
+#ifndef PL_NAMESPACE
+#define PL_NAMESPACE plicp2
+#endif
+
+namespace PL_NAMESPACE {
 
 constexpr int NSUM = 16;  // 14 GPC sums + total_error + pad
+
+// thread within its job / the job's slot within the CTA / barriers and votes over the T threads of one job
+template <int T>
+__device__ __forceinline__ int pl_tid() { return PLICP_NS == 1 ? (int)threadIdx.x : (int)(threadIdx.x % T); }
+template <int T>
+__device__ __forceinline__ int pl_slot() { return PLICP_NS == 1 ? 0 : (int)(threadIdx.x / T); }
+template <int T>
+__device__ __forceinline__ void pl_sync() {
+    if (PLICP_NS == 1) __syncthreads();
+    else asm volatile("bar.sync %0, %1;" ::"r"(pl_slot<T>() + 1), "r"(T) : "memory");  // barrier 0 stays the CTA's
+}
+template <int T>
+__device__ __forceinline__ int pl_sync_or(int v) {
+    if (PLICP_NS == 1) return __syncthreads_or(v);
+    int r;
+    asm volatile("{\n\t"
+                 ".reg .pred p, q;\n\t"
+                 "setp.ne.s32 p, %1, 0;\n\t"
+                 "bar.red.or.pred q, %2, %3, p;\n\t"
+                 "selp.s32 %0, 1, 0, q;\n\t"
+                 "}" : "=r"(r) : "r"(v), "r"(pl_slot<T>() + 1), "r"(T) : "memory");
+    return r;
+}
 
 struct Ctl {
     unsigned long long mbar;  // mbarrier of the bulk (TMA) copy that brings the jump tables back (PLICP_TMA_JT builds)
@@ -54,6 +90,7 @@ struct Lay {
     unsigned cj2;    // short[n]
     unsigned spec;   // short[n] last_best each ray was (or will be) searched with
     unsigned jt;     // short[2][n][2] pairs (up_bigger, up_smaller)[n], (down_bigger, down_smaller)[n]
+    unsigned msctl;  // int[4], multi-slot layout only: [0] slots that are done with the shared arrays, [1] covariance turn lock
     unsigned total;
     bool jt_shared;  // hist/candi lie on top of jt: the jump tables are copied in again before every search
 };
@@ -80,11 +117,46 @@ __host__ __device__ inline Lay make_layout(int n, int nthreads) {
     l.spec = o;  o += align16(2u * un);
     l.jt = o;    o += align16(8u * un);
     if (l.jt_shared) { l.hist = l.jt; l.candi = l.jt + 4u * 768; }
+    l.msctl = 0;
     l.total = align16(o);
     return l;
 }
 
-__host__ __device__ inline size_t smem_bytes(int n, int nthreads) { return make_layout(n, nthreads).total; }
+// The multi-slot layout (PLICP_NS jobs per CTA): [refp | sensr | rr2 | jt] once, then per slot [d2j | red | ctl | hist |
+// candi | cj1 | cj2 | spec].  The jump tables stay in place for the whole job (the histograms have their own bytes), so
+// nothing is copied in again before a search.  92 n + 30 KB at four slots: 218 KB at 2048 beams.  The covariance (plicp2_cov.cuh)
+// takes rr2 and jt as scratch: a slot computes it only when all slots are done iterating, one slot at a time (msctl).
+__host__ __device__ inline unsigned slot_bytes(int n, int nthreads) {
+    const unsigned nw = (unsigned)(nthreads + 31) / 32, un = (unsigned)n;
+    return align16(8u * un) + 8u * nw * NSUM + align16((unsigned)sizeof(Ctl)) + 4u * 768 + 2u * 1536 + 3u * align16(2u * un);
+}
+__host__ __device__ inline Lay make_layout_slots(int n, int nthreads, int nslots, int slot) {
+    const unsigned nw = (unsigned)(nthreads + 31) / 32, un = (unsigned)n;
+    Lay l;
+    unsigned o = 0;
+    l.refp = o;  o += 16u * un;
+    l.sensr = o; o += align16(4u * un);
+    l.rr2 = o;   o += align16(8u * un);
+    l.jt = o;    o += align16(8u * un);
+    l.msctl = o; o += 16u;
+    const unsigned per = slot_bytes(n, nthreads);
+    l.total = align16(o + per * (unsigned)nslots);
+    o += per * (unsigned)slot;
+    l.d2j = o;   o += align16(8u * un);
+    l.red = o;   o += 8u * nw * NSUM;
+    l.ctl = o;   o += align16((unsigned)sizeof(Ctl));
+    l.hist = o;  o += 4u * 768;
+    l.candi = o; o += 2u * 1536;
+    l.cj1 = o;   o += align16(2u * un);
+    l.cj2 = o;   o += align16(2u * un);
+    l.spec = o;
+    l.jt_shared = false;
+    return l;
+}
+
+__host__ __device__ inline size_t smem_bytes(int n, int nthreads) {
+    return PLICP_NS == 1 ? make_layout(n, nthreads).total : make_layout_slots(n, nthreads, PLICP_NS, 0).total;
+}
 
 extern __shared__ __align__(16) unsigned char smem_raw[];
 #define PL_SH(type, off) (reinterpret_cast<type *>(smem_raw + (off)))
@@ -165,4 +237,4 @@ __device__ __forceinline__ double reading_of(float r_cm, const LaserDev &L, cons
     return m;
 }
 
-}  // namespace plicp2
+}  // namespace PL_NAMESPACE

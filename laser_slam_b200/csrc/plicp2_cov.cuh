@@ -13,7 +13,7 @@
 #pragma once
 #include "plicp2_common.cuh"
 
-namespace plicp2 {
+namespace PL_NAMESPACE {
 
 // C_k = n n' with n = (cos a, sin a), a = pi/2 + atan2(j1y - j2y, j1x - j2x)
 __device__ __forceinline__ void compute_C_k(double j1x, double j1y, double j2x, double j2y, double C[3]) {
@@ -43,18 +43,18 @@ __device__ __forceinline__ double quad2(double ux, double uy, const double C[3],
 template <int T, int NV>
 __device__ __forceinline__ void block_sum_f64(double (&v)[NV], double *red, double (&out)[NV]) {
     constexpr int NW = T / 32;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31, warp = pl_tid<T>() >> 5;
 #pragma unroll
     for (int q = 0; q < NV; q++) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) v[q] += __shfl_down_sync(0xffffffffu, v[q], o);
     }
-    __syncthreads();  // red may still be read by a previous user
+    pl_sync<T>();  // red may still be read by a previous user
     if (lane == 0) {
 #pragma unroll
         for (int q = 0; q < NV; q++) red[warp * NSUM + q] = v[q];
     }
-    __syncthreads();
+    pl_sync<T>();
 #pragma unroll
     for (int q = 0; q < NV; q++) {
         double s = 0;
@@ -84,15 +84,15 @@ __device__ __forceinline__ bool inv3(const double A[3][3], double inv[3][3]) {
 template <int T>
 __device__ __forceinline__ void covariance_exact(const Lay &l, int n, int C, const double2 *cs_table, double x0,
                                                  double x1, double ct, double st, double sigma, double cov[6]) {
-    const int t = threadIdx.x;
+    const int t = pl_tid<T>();
     const double2 *refp = PL_SH(const double2, l.refp);
     const float *sensr = PL_SH(const float, l.sensr);
     const short *cj1 = PL_SH(const short, l.cj1), *cj2 = PL_SH(const short, l.cj2);
     double *g1x = PL_SH(double, l.rr2), *g1y = PL_SH(double, l.d2j), *g1t = PL_SH(double, l.jt);
     double *red = PL_SH(double, l.red);
-    __syncthreads();  // everybody is done with rr2 / d2j / jt
+    pl_sync<T>();  // everybody is done with rr2 / d2j / jt
     for (int j = t; j < n; j += T) { g1x[j] = 0; g1y[j] = 0; g1t[j] = 0; }
-    __syncthreads();
+    pl_sync<T>();
     double acc[12];
 #pragma unroll
     for (int q = 0; q < 12; q++) acc[q] = 0;
@@ -168,4 +168,4 @@ __device__ __forceinline__ void covariance_exact(const Lay &l, int n, int C, con
         for (int b = a; b < 3; b++) cov[q++] = s2 * (Tm[a][0] * Hi[b][0] + Tm[a][1] * Hi[b][1] + Tm[a][2] * Hi[b][2]);
 }
 
-}  // namespace plicp2
+}  // namespace PL_NAMESPACE

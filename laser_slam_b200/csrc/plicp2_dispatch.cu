@@ -8,6 +8,7 @@ cudaError_t plicp_launch_t128(const PlicpArgs &a, cudaStream_t st);
 cudaError_t plicp_launch_t192(const PlicpArgs &a, cudaStream_t st);
 cudaError_t plicp_launch_t256(const PlicpArgs &a, cudaStream_t st);
 cudaError_t plicp_launch_t512(const PlicpArgs &a, cudaStream_t st);
+cudaError_t plicp_launch_ms128(const PlicpArgs &a, cudaStream_t st);
 
 // CTA size per beam count: as many resident CTAs per SM as the shared-memory footprint (~51 B per beam) and the
 // registers allow -- a job has serial stretches (the solve, the tail of a search round) that only other jobs on the
@@ -60,6 +61,12 @@ cudaError_t plicp_launch(const PlicpArgs &a, int sm_count, cudaStream_t st, int 
     if (!a.jt || !a.owner) return cudaErrorInvalidValue;
     cudaError_t e = plicp_jump_launch(a, const_cast<short *>(a.jt), const_cast<int32_t *>(a.owner), st, launched);
     if (e != cudaSuccess) return e;
+    if (a.ns == 4) {
+        if (T != 128) return cudaErrorInvalidValue;
+        e = plicp_launch_ms128(a, st);
+        if (e == cudaSuccess && launched) *launched += 1;
+        return e;
+    }
     e = T == 128 ? plicp_launch_t128(a, st) : T == 192 ? plicp_launch_t192(a, st) : T == 256 ? plicp_launch_t256(a, st) : plicp_launch_t512(a, st);
     if (e == cudaSuccess && launched) *launched += 1;
     return e;

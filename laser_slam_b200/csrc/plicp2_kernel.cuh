@@ -8,7 +8,7 @@
 #include "plicp2_select.cuh"
 #include "plicp2_solve.cuh"
 
-namespace plicp2 {
+namespace PL_NAMESPACE {
 
 // Which instances carry the list of unfinished walks (plicp2_search.cuh: a walk that outlives its budgets is finished
 // warp-wide after the round's barrier).  PLICP_LIST_MIN_T: tuning builds.
@@ -153,8 +153,8 @@ static __device__ __noinline__ int finish_unfinished(const Lay l, const WalkCtx 
             PL_SH(short, l.cj2)[i] = (short)(r1 >= 0 ? j2 : -1);
         }
     }
-    __syncthreads();
-    if (threadIdx.x == 0) { ctl->npend = 0; ctl->pend_next = 0; }  // the next round of walks is at least one more barrier away
+    pl_sync<T>();
+    if (pl_tid<T>() == 0) { ctl->npend = 0; ctl->pend_next = 0; }  // the next round of walks is at least one more barrier away
     return changed;
 }
 
@@ -197,7 +197,7 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
                                                          const PendRef<kList<T>> &pr, WalkDiag &dg,
                                                          PhaseClock &pc, JtPrefetch &tma STATS_PARAM) {
     constexpr int NW = T / 32;
-    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int t = pl_tid<T>(), lane = t & 31, warp = t >> 5;
     const int n = w.n;
     const unsigned lane_lt = (1u << lane) - 1u;
     Ctl *ctl = PL_SH(Ctl, l.ctl);
@@ -211,7 +211,7 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
         } else {
             uint2 *dst = PL_SH(uint2, l.jt);
             for (int q = t; q < n; q += T) dst[q] = __ldcs(jt_src + q);  // streaming: leave the L1 to the cs table
-            __syncthreads();
+            pl_sync<T>();
         }
     }
     if (!chunked) {
@@ -247,7 +247,7 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
             }
         }
     }
-    __syncthreads();
+    pl_sync<T>();
     process_pending<T>(l, w, it, pr);
     pc.mark(2);
     short *cj1 = PL_SH(short, l.cj1);
@@ -265,7 +265,7 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
             const int last = __shfl_sync(0xffffffffu, c1, vm ? 31 - __clz(vm) : 0);
             if (lane == 0) glast[k * NW + warp] = (short)(vm ? last : -1);
         }
-        __syncthreads();
+        pl_sync<T>();
 #pragma unroll 1
         for (int k = 0; k < C; k++) {
             const int i = k * T + t;
@@ -292,7 +292,7 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
                 if (need) queue[base + __popc(m & lane_lt)] = (short)i;
             }
         }
-        __syncthreads();
+        pl_sync<T>();
         const int total = *qn;
         if (total == 0) break;
         dg.rounds++;
@@ -306,10 +306,10 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
             else unfinished = 1;  // on the list: process_pending says whether its j1 changed
         }
         // the usual end: nothing changed and nothing is unfinished -- last_best of every ray is what it was walked with
-        if (!__syncthreads_or(changed | unfinished)) break;
+        if (!pl_sync_or<T>(changed | unfinished)) break;
         if constexpr (kList<T>) {
             changed |= process_pending<T>(l, w, it, pr);
-            if (!__syncthreads_or(changed)) break;
+            if (!pl_sync_or<T>(changed)) break;
         }
     }
     pc.mark(3);
@@ -324,13 +324,14 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
 #define PLICP_MINB_192 4   // resident CTAs per SM the 192-thread instance is compiled for (80 registers); tuning builds: 3
 #endif
 template <int T>
-__global__ void __launch_bounds__(T, (T <= 192 ? PLICP_MINB_192 : T <= 288 ? 2 : 1)) plicp2_kernel(PlicpArgs a) {
+__global__ void __launch_bounds__(T * PLICP_NS, (PLICP_NS > 1 ? 1 : T <= 192 ? PLICP_MINB_192 : T <= 288 ? 2 : 1))
+plicp2_kernel(PlicpArgs a) {
     constexpr int NW = T / 32;
     const int n = a.L.n;
     const int C = (n + T - 1) / T;
-    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-    const int job = blockIdx.x;
-    const Lay l = make_layout(n, T);
+    const int t = pl_tid<T>(), lane = t & 31, warp = t >> 5;
+    const int job = PLICP_NS == 1 ? (int)blockIdx.x : (int)blockIdx.x * PLICP_NS + pl_slot<T>();
+    const Lay l = PLICP_NS == 1 ? make_layout(n, T) : make_layout_slots(n, T, PLICP_NS, pl_slot<T>());
     Ctl *ctl = PL_SH(Ctl, l.ctl);
     const LaserDev L = a.L;
     const zhsm_plicp_params &P = a.P;
@@ -343,9 +344,21 @@ __global__ void __launch_bounds__(T, (T <= 192 ? PLICP_MINB_192 : T <= 288 ? 2 :
 
     PhaseClock pc;
     pc.start();
+    volatile int *msctl = PL_SH(volatile int, l.msctl);
+    if (PLICP_NS > 1 && threadIdx.x == 0) { msctl[0] = 0; msctl[1] = 0; }  // ordered before any use by the CTA-wide barrier
     // ---------------- load + fromPMScan2LDP + ld_valid_fields + ld_invalid_if_outside + ld_compute_cartesian
     const int ref_i = a.ref_idx[job], sens_i = a.sens_idx[job];
-    if ((unsigned)ref_i >= (unsigned)a.S || (unsigned)sens_i >= (unsigned)a.S) {
+    bool bad_job = (unsigned)ref_i >= (unsigned)a.S || (unsigned)sens_i >= (unsigned)a.S;
+    if (PLICP_NS > 1) {
+        // The CTA's jobs must share both scans (the caller's promise: ZHSM_MULTISTART); a job that does not is failed,
+        // loudly, instead of being matched against the wrong scans.  Its threads still take part in the one CTA-wide
+        // barrier below.  The shared arrays are filled from slot 0's scans, by every slot (the same values).
+        const int ref0 = a.ref_idx[blockIdx.x * PLICP_NS], sens0 = a.sens_idx[blockIdx.x * PLICP_NS];
+        bad_job = bad_job || ref_i != ref0 || sens_i != sens0;
+        if ((unsigned)ref0 >= (unsigned)a.S || (unsigned)sens0 >= (unsigned)a.S) bad_job = true;  // (uniform over the CTA)
+        if (bad_job) __syncthreads();
+    }
+    if (bad_job) {
         // device-resident job lists are not checked by the host: a bad index fails its own job, never the batch
         if (t == 0) {
             zhsm_result r = {};
@@ -353,6 +366,7 @@ __global__ void __launch_bounds__(T, (T <= 192 ? PLICP_MINB_192 : T <= 288 ? 2 :
             a.results[job] = r;
         }
         if (a.corr_j1) for (int i = t; i < n; i += T) { a.corr_j1[(size_t)job * n + i] = -1; a.corr_j2[(size_t)job * n + i] = -1; }
+        if (PLICP_NS > 1 && t == 0) atomicAdd((int *)&msctl[0], 1);  // this slot never reads the shared arrays
         return;
     }
     const float *ref_row = a.scans + (size_t)ref_i * n;
@@ -378,7 +392,7 @@ __global__ void __launch_bounds__(T, (T <= 192 ? PLICP_MINB_192 : T <= 288 ? 2 :
         tma.bytes = 8u * (unsigned)n;
         tma.src = jt_job;
         if (t == 0) mbar_init(tma.mbar, 1);
-        __syncthreads();   // the barrier object is initialised before anyone arms or polls it
+        pl_sync<T>();   // the barrier object is initialised before anyone arms or polls it
         tma.issue();       // the first search's tables travel while the scans are loaded and converted
     }
 #endif
@@ -400,6 +414,7 @@ __global__ void __launch_bounds__(T, (T <= 192 ? PLICP_MINB_192 : T <= 288 ? 2 :
         cj2[i] = -1;
         PL_SH(short, l.spec)[i] = -1;
     }
+    if (PLICP_NS > 1) __syncthreads();  // the one CTA-wide barrier: the shared arrays are complete (every slot wrote them)
     if (t == 0) {
         ctl->topbyte = 0x3f;
         ctl->npend = 0;
@@ -410,7 +425,7 @@ __global__ void __launch_bounds__(T, (T <= 192 ? PLICP_MINB_192 : T <= 288 ? 2 :
         ctl->sn[0] = sin(ctl->x[0][2]);
     }
     const int tot = block_sum<T>((nvf_ref << 16) | nvf_sens, ctl->ired, 0);
-    const int tot_bad = __syncthreads_or(bad_field);
+    const int tot_bad = pl_sync_or<T>(bad_field);
     const int tot_ref = tot >> 16, tot_sens = tot & 0xffff;
     zhsm_result *res = a.results + job;
     int16_t *oj1 = a.corr_j1 ? a.corr_j1 + (size_t)job * n : nullptr;
@@ -427,6 +442,7 @@ __global__ void __launch_bounds__(T, (T <= 192 ? PLICP_MINB_192 : T <= 288 ? 2 :
         }
         if (oj1) for (int i = t; i < n; i += T) { oj1[i] = -1; oj2[i] = -1; }
         tma.wait();  // nothing may be in flight into this CTA's shared memory when it exits
+        if (PLICP_NS > 1 && t == 0) atomicAdd((int *)&msctl[0], 1);
         return;
     }
     pc.mark(0);  // the block sums above were barriers: the tables are in place
@@ -480,7 +496,7 @@ __global__ void __launch_bounds__(T, (T <= 192 ? PLICP_MINB_192 : T <= 288 ? 2 :
             valid = find_correspondences<T>(l, wc, it, C, sens, iteration < a.chunk_iters, jt_src, pr, dg, pc, tma STATS_ARG);
             if (P.outliers_remove_doubles) {
                 for (int j = t; j < n; j += T) d2j[j] = BIG;  // the search used this area as its queue
-                __syncthreads();
+                pl_sync<T>();
             }
             // kill_outliers_double (icp_outliers.c): min dist2_j1 per ref index.  dist2_j1 is recomputed
             // from the same operands the walk used (bit-identical), so it needs no storage.
@@ -657,7 +673,7 @@ __global__ void __launch_bounds__(T, (T <= 192 ? PLICP_MINB_192 : T <= 288 ? 2 :
                     }
                 }
             }
-            __syncthreads();
+            pl_sync<T>();
             pc.mark(8);
             // loop control of icp_loop, evaluated identically by every thread
             const int st = ctl->solve_status;
@@ -716,21 +732,21 @@ __global__ void __launch_bounds__(T, (T <= 192 ? PLICP_MINB_192 : T <= 288 ? 2 :
             ctl->next = next;
             ctl->fin = valid_out | (restarted << 1);
         }
-        __syncthreads();
+        pl_sync<T>();
         if (!ctl->next) break;
     }
     pc.mark(9);
     // ---------------- final correspondences + result record
     const int fin = ctl->fin;
     const bool v_ok = fin & 1, v_restarted = fin & 2;
-    __syncthreads();
+    pl_sync<T>();
     if (v_ok) {
         if (t == 0) {
             for (int k = 0; k < 3; k++) ctl->x[0][k] = best_x[k];
             ctl->cs[0] = cos(best_x[2]);
             ctl->sn[0] = sin(best_x[2]);
         }
-        __syncthreads();
+        pl_sync<T>();
         it.x0 = ctl->x[0][0];
         it.x1 = ctl->x[0][1];
         it.cs = ctl->cs[0];
@@ -748,29 +764,48 @@ __global__ void __launch_bounds__(T, (T <= 192 ? PLICP_MINB_192 : T <= 288 ? 2 :
         if (!cv) { cj1[i] = -1; cj2[i] = -1; }
         if (oj1) { oj1[i] = cj1[i]; oj2[i] = cj2[i]; }
     }
-    __syncthreads();
+    pl_sync<T>();
     {
         unsigned hc = corr_hash_chunk(l, n, t, a.hash_chunk, a.hashmat);
         hc = __reduce_xor_sync(0xffffffffu, hc);
         if (lane == 0 && hc) atomicXor(&ctl->hash_acc[0], hc);
     }
-    __syncthreads();
+    pl_sync<T>();
     const int walks_all = block_sum<T>(dg.walks, ctl->ired, 0);
 
     const int walks_first = block_sum<T>(dg.first, ctl->ired, 1);
     const int steps_all = block_sum<T>(dg.steps, ctl->ired, 2) + ctl->steps_pend;
 #ifdef PLICP_WALK_STATS
     int sts[5];
-    for (int k = 0; k < 5; k++) sts[k] = block_sum<T>(st_arr[k], ctl->ired, k & 3), __syncthreads();
+    for (int k = 0; k < 5; k++) sts[k] = block_sum<T>(st_arr[k], ctl->ired, k & 3), pl_sync<T>();
     int stmax = st_arr[5];
     for (int o = 16; o > 0; o >>= 1) stmax = max(stmax, __shfl_xor_sync(0xffffffffu, stmax, o));
     if (lane == 0) atomicMax(&ctl->qn[0], stmax);
-    __syncthreads();
+    pl_sync<T>();
     stmax = ctl->qn[0];
 #endif
     double cov[6] = {0, 0, 0, 0, 0, 0};
-    if (v_ok && P.do_compute_covariance)
+    if (PLICP_NS > 1) {  // this slot has read rr2 and the jump tables for the last time
+        pl_sync<T>();
+        if (t == 0) { __threadfence_block(); atomicAdd((int *)&msctl[0], 1); }
+    }
+    if (v_ok && P.do_compute_covariance) {
+        if (PLICP_NS > 1) {
+            // The covariance takes the SHARED rr2 and jt areas as scratch: wait until every slot of the CTA is done
+            // with them, then take the turn.  The slots run independently, so the wait always ends.
+            if (t == 0) {
+                while (msctl[0] < PLICP_NS) __nanosleep(200);
+                while (atomicCAS((int *)&msctl[1], 0, 1) != 0) __nanosleep(200);
+                __threadfence_block();
+            }
+            pl_sync<T>();
+        }
         covariance_exact<T>(l, n, C, a.cs, it.x0, it.x1, it.cs, it.sn, P.sigma, cov);
+        if (PLICP_NS > 1) {
+            pl_sync<T>();
+            if (t == 0) { __threadfence_block(); atomicExch((int *)&msctl[1], 0); }
+        }
+    }
     if (t == 0) {
         zhsm_result r = {};
         r.valid = valid_out;
@@ -812,4 +847,4 @@ __global__ void __launch_bounds__(T, (T <= 192 ? PLICP_MINB_192 : T <= 288 ? 2 :
     }
 }
 
-}  // namespace plicp2
+}  // namespace PL_NAMESPACE

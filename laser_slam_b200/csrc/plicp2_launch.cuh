@@ -1,12 +1,14 @@
-// laser_slam_b200/csrc/plicp2_launch.cuh -- launch helper shared by the per-CTA-size instance files.
+// laser_slam_b200/csrc/plicp2_launch.cuh -- launch helper shared by the instance files: one CTA of TT threads per job, or
+// (PLICP_NS > 1, the multi-start instance) one CTA of PLICP_NS * TT threads per PLICP_NS jobs that share their scans.
 #pragma once
 #define PLICP2_LAUNCH(TT)                                                                                        \
     {                                                                                                            \
-        size_t smem = plicp2::smem_bytes(a.L.n, TT);                                                             \
+        size_t smem = PL_NAMESPACE::smem_bytes(a.L.n, TT);                                                       \
         smem += (size_t)a.smem_pad; /* tuning (ZHSM_PLICP_SMEM_PAD, read in zhsm_create): fewer CTAs per SM */    \
-        cudaError_t e = cudaFuncSetAttribute(plicp2::plicp2_kernel<TT>,                                          \
+        if (smem > 227 * 1024 || a.B % PLICP_NS != 0) return cudaErrorInvalidValue;                              \
+        cudaError_t e = cudaFuncSetAttribute(PL_NAMESPACE::plicp2_kernel<TT>,                                    \
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);            \
         if (e != cudaSuccess) return e;                                                                          \
-        plicp2::plicp2_kernel<TT><<<a.B, TT, smem, st>>>(a);                                                     \
+        PL_NAMESPACE::plicp2_kernel<TT><<<a.B / PLICP_NS, TT * PLICP_NS, smem, st>>>(a);                         \
         return cudaGetLastError();                                                                               \
     }

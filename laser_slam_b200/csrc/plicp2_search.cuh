@@ -20,7 +20,7 @@
 #pragma once
 #include "plicp2_common.cuh"
 
-namespace plicp2 {
+namespace PL_NAMESPACE {
 
 struct Ray {
     double wx, wy;    // ld_compute_world_coords: R(x_old[2]) p + x_old[0:2]
@@ -544,4 +544,4 @@ static __device__ __noinline__ int walk_warp_both(const WalkCtx c, const RayU u,
     return nwin;
 }
 
-}  // namespace plicp2
+}  // namespace PL_NAMESPACE

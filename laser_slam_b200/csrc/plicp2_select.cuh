@@ -2,7 +2,7 @@
 #pragma once
 #include "plicp2_common.cuh"
 
-namespace plicp2 {
+namespace PL_NAMESPACE {
 
 // Block-wide integer sum, result to every thread, ONE barrier.  `slot` selects one of 4 scratch rows; a row must
 // not be reused until another barrier has passed (callers alternate rows).
@@ -10,8 +10,8 @@ template <int T>
 __device__ __forceinline__ int block_sum(int v, int *ired, int slot) {
     constexpr int NW = T / 32;
     int w = __reduce_add_sync(0xffffffffu, v);
-    if ((threadIdx.x & 31) == 0) ired[slot * 16 + (threadIdx.x >> 5)] = w;
-    __syncthreads();
+    if ((threadIdx.x & 31) == 0) ired[slot * 16 + (pl_tid<T>() >> 5)] = w;
+    pl_sync<T>();
     int tot = 0;
 #pragma unroll
     for (int i = 0; i < NW; i++) tot += ired[slot * 16 + i];
@@ -78,7 +78,7 @@ __device__ __forceinline__ void locate2(const int *hist, int lane, const int rem
 template <int T, class Clock>
 __device__ __forceinline__ void select2(const Lay &l, int C, unsigned valid, int rank0, int rank1, int top_guess,
                                         const int *nbelow_p, double &v0, double &v1, Clock &pc) {
-    const int t = threadIdx.x, lane = t & 31;
+    const int t = pl_tid<T>(), lane = t & 31;
     const unsigned long long *keyS = PL_SH(const unsigned long long, l.d2j);
     int *hist_all = PL_SH(int, l.hist);
     short *cand_all = PL_SH(short, l.candi);
@@ -87,7 +87,7 @@ __device__ __forceinline__ void select2(const Lay &l, int C, unsigned valid, int
     bool done[2] = {false, false};
     double val[2] = {0, 0};
     int first_pass = 0;
-    __syncthreads();  // the keys, their histogram (set 1) and *nbelow_p are in place
+    pl_sync<T>();  // the keys, their histogram (set 1) and *nbelow_p are in place
     pc.mark(18);
     {
         const int nbelow = *nbelow_p;
@@ -107,7 +107,7 @@ __device__ __forceinline__ void select2(const Lay &l, int C, unsigned valid, int
                 }
             }
         } else {
-            __syncthreads();  // slow warps may still be reading set 1, which pass 0 is about to zero
+            pl_sync<T>();  // slow warps may still be reading set 1, which pass 0 is about to zero
         }
     }
     pc.mark(19);
@@ -130,7 +130,7 @@ __device__ __forceinline__ void select2(const Lay &l, int C, unsigned valid, int
             if (m0) cand[digit] = (short)i;
             if (m1) cand[256 + digit] = (short)i;
         }
-        __syncthreads();
+        pl_sync<T>();
         pc.mark(18);
         int digit[2], nrem[2], cnt[2], total[2];
         locate2(hist, lane, rem, digit, nrem, cnt, total);
@@ -180,4 +180,4 @@ __device__ __forceinline__ unsigned corr_hash_chunk(const Lay &l, int n, int t, 
     return out;
 }
 
-}  // namespace plicp2
+}  // namespace PL_NAMESPACE

@@ -7,7 +7,11 @@
 #pragma once
 #include <math.h>
 
-namespace plicp2 {
+#ifndef PL_NAMESPACE
+#define PL_NAMESPACE plicp2  // (plicp2_common.cuh: one namespace per instance file)
+#endif
+
+namespace PL_NAMESPACE {
 
 __device__ __forceinline__ double poly_eval(const double *c, int deg, double x) {
     double v = c[deg];
@@ -304,4 +308,4 @@ __device__ __forceinline__ void pose_diff(const double pose2[3], const double po
     while (res[2] < -PI) res[2] += 2 * PI;
 }
 
-}  // namespace plicp2
+}  // namespace PL_NAMESPACE

@@ -130,6 +130,7 @@ extern "C" void zhsm_destroy(zhsm_handle *h) {
     if (h->d_co) cudaFree(h->d_co);
     if (h->d_cs) cudaFree(h->d_cs);
     if (h->d_hashmat) cudaFree(h->d_hashmat);
+    if (h->d_hashmat_ms) cudaFree(h->d_hashmat_ms);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     if (h->ev_busy) cudaEventDestroy(h->ev_busy);
@@ -204,6 +205,14 @@ extern "C" zhsm_status zhsm_set_laser(zhsm_handle *h, const zhsm_laser *laser) {
         h->hash_chunk = ch;
         h->hash_T = T;  // the launch uses exactly the shape these matrices were built for
         h->hash_C = C;
+        // ... and for the multi-start instance (128 threads per job)
+        int ch_ms = (n + 127) / 128;
+        if (ch_ms & 1) ch_ms++;
+        plicp_build_hash_matrices(n, 128, ch_ms, mat);
+        if (h->d_hashmat_ms) { cudaFree(h->d_hashmat_ms); h->d_hashmat_ms = nullptr; }
+        ZHSM_CUDA_TRY(h, cudaMalloc(&h->d_hashmat_ms, sizeof(uint32_t) * mat.size()));
+        ZHSM_CUDA_TRY(h, cudaMemcpy(h->d_hashmat_ms, mat.data(), sizeof(uint32_t) * mat.size(), cudaMemcpyHostToDevice));
+        h->hash_chunk_ms = ch_ms;
     }
     h->laser = *laser;
     h->have_laser = true;
@@ -334,6 +343,15 @@ extern "C" zhsm_status zhsm_plicp_batch(zhsm_handle *h, const float *scans, int 
     a.hashmat = h->d_hashmat;
     a.hash_chunk = h->hash_chunk;
     a.chunk_iters = h->knob_chunk_iters;
+    // ZHSM_MULTISTART: the caller promises jobs in runs of four that share both scans (pair-major multi-start).  Used
+    // where it pays: long scans, whose single-job CTAs fit only twice per SM.  The kernel re-checks the promise per job.
+    if ((flags & ZHSM_MULTISTART) && B % 4 == 0 && n > 1472 && plicp_ms128_smem_bytes(n) <= 227 * 1024 && (n + 127) / 128 <= 32 &&
+        h->knob_T == 0) {
+        a.ns = 4;
+        a.T = 128;
+        a.hashmat = h->d_hashmat_ms;
+        a.hash_chunk = h->hash_chunk_ms;
+    }
 
     // ld_valid_fields' per-scan-geometry checks (laser_data.c): nrays, fov, theta[] consistent by construction
     {

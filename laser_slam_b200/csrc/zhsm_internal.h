@@ -30,6 +30,8 @@ struct zhsm_handle {
     int knob_chunk_iters = 2;  // ZHSM_PLICP_CHUNK_ITERS: first iterations searched in chunk order
     int knob_smem_pad = 0;     // ZHSM_PLICP_SMEM_PAD: extra dynamic shared memory (fewer CTAs per SM)
     int hash_T = 0, hash_C = 0;  // CTA shape the hash matrices were built for (zhsm_set_laser)
+    uint32_t *d_hashmat_ms = nullptr;  // the same for the multi-start instance's shape (128 threads per job)
+    int hash_chunk_ms = 0;
 
     bool have_laser = false;
     zhsm_laser laser{};
@@ -79,6 +81,7 @@ struct PlicpArgs {
                              // when job k is the OWNER of that scan (lowest job of the launch that uses it)
     const int32_t *owner;    // [S] per scan: the owning job of this launch (jobs sharing a ref scan share its tables)
     int S;                   // scans in the pool (device-side range check of the job indices)
+    int ns;                  // 4: the multi-start instance (four jobs per CTA that share both scans, 128 threads each); else 1
     int T;                   // CTA shape the handle's hash matrices were built for
     int smem_pad;            // tuning: extra dynamic shared memory per CTA
     const uint32_t *hashmat; // [T][32] GF(2) matrices of the parallel ld_corr_hash (plicp2_select.cuh)
@@ -125,6 +128,7 @@ cudaError_t corridor_launch(const float *scans, const unsigned char *bad, const 
 zhsm_status zhsm_stage(zhsm_handle *h, int slot, size_t bytes, void **out);
 
 cudaError_t plicp_launch(const PlicpArgs &a, int sm_count, cudaStream_t st, int *launched);
+size_t plicp_ms128_smem_bytes(int n);  // dynamic shared memory of the multi-start instance (4 jobs per CTA)
 size_t plicp_jump_bytes_per_job(int n);
 // CTA shape the PL-ICP kernel uses for n beams: T threads, C rays per thread, hash chunk (even) per thread
 void plicp_shape(int n, int knob_T, int *T, int *C, int *hash_chunk);

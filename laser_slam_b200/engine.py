@@ -106,7 +106,7 @@ RESULT_DTYPE = np.dtype([("x", "f8", 3), ("cov", "f8", 6), ("error", "f8"), ("va
 assert RESULT_DTYPE.itemsize == 128
 
 SCANS_ON_DEVICE, JOBS_ON_DEVICE, RESULTS_ON_DEVICE, ALL_ON_DEVICE = 1, 2, 4, 7
-FILTER_SCANS, WRITEBACK_SCANS = 8, 16
+FILTER_SCANS, WRITEBACK_SCANS, MULTISTART = 8, 16, 32
 ALGO_PSM, ALGO_PM_ICP, ALGO_PSM_ICP, ALGO_FMATCH = 0, 1, 2, 3
 BEST_GOODNESS, BEST_MEAN_ERROR = 0, 1
 LASER_UTM_GATE = 1  # zhsm_laser.flags: pm_orientation_search's HOKUYO_UTM_30LX branch
@@ -275,7 +275,7 @@ class Engine:
         return scans
 
     def plicp(self, scans, ref_idx, sens_idx, first_guess=None, params=None, results=None, want_corr=False,
-              stream=None, filter_scans=False, writeback=False):
+              stream=None, filter_scans=False, writeback=False, multistart=False):
         """Batched CCanonicalMatcher::FMatch on median-filtered scans.  Host (numpy) or device (torch) buffers;
         all job arrays must live on the same side."""
         n = self.laser.n
@@ -285,6 +285,7 @@ class Engine:
         S = int(scans.shape[0])
         flags = (SCANS_ON_DEVICE if dev_scans else 0) | (JOBS_ON_DEVICE if dev_jobs else 0)
         flags |= (FILTER_SCANS if filter_scans else 0) | (WRITEBACK_SCANS if writeback else 0)
+        flags |= MULTISTART if multistart else 0   # jobs in runs of four that share both scans (see zhsm.h)
         _same_side("plicp: ref_idx / sens_idx / first_guess", ref_idx, sens_idx, first_guess)
         if not dev_scans:
             assert scans.dtype == np.float32 and scans.flags.c_contiguous and scans.shape[1] == n

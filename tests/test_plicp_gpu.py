@@ -322,3 +322,76 @@ def test_engine_rejects_malformed_device_tensors():
     eng.sync()
     assert (res.cpu().numpy().view(zh.RESULT_DTYPE).reshape(-1)["valid"] == 1).all()
     eng.close()
+
+
+def _same_records(a, b, with_cov):
+    """Two CTA shapes of the kernel on the same jobs: every integer of the record equal (valid, status, iterations, nvalid,
+    correspondence hash, loops), pose and error equal to rounding (the 14 GPC sums are added in a tree whose shape follows
+    the thread count: <= 1e-12 m), covariance to 1e-6 (shared-memory atomics)."""
+    for f in ("valid", "status", "iterations", "nvalid", "corr_hash", "n_loops"):
+        assert np.array_equal(a[f], b[f]), (f, np.flatnonzero(a[f] != b[f])[:10])
+    assert np.abs(a["x"] - b["x"]).max() <= 1e-12 and np.allclose(a["error"], b["error"], rtol=1e-10, atol=0)
+    if with_cov:
+        assert np.allclose(a["cov"], b["cov"], rtol=1e-6, atol=1e-15)
+
+
+def test_multistart_instance_same_records_and_checks_its_promise():
+    """ZHSM_MULTISTART (include/zhsm.h): four jobs that share both scans per CTA over one staged copy of the scans
+    (plicp2_ms128.cu).  On 2048-beam multi-start jobs with poor first guesses (the long-walk code runs in it) the records
+    must be those of the single-job instance (_same_records), with and without the covariance; shorter scans ignore the
+    flag; a run of four that does NOT share its scans fails those jobs (ZHSM_JOB_INVALID_SCAN) and nothing else."""
+    import torch
+    import laser_slam_b200 as zh
+    P, G, n = 24, 16, 2048
+    PM_PI = 3.141592654
+    lz = zh.Laser()
+    lz.n = n; lz.fi_min = np.float32(-PM_PI); lz.dfi = np.float32((360 * PM_PI / 180) / (n - 1.0))
+    lz.min_range_cm = 10; lz.max_range_cm = 3000; lz.min_valid_points = n // 5; lz.scan_window = n // 10
+    eng = zh.Engine(0)
+    try:
+        eng.set_laser(lz)
+        dev = torch.device("cuda:0")
+        d_scans = torch.empty((2 * P, n), dtype=torch.float32, device=dev)
+        d_truth = torch.empty((P, 3), dtype=torch.float64, device=dev)
+        eng.synth_pairs(d_scans, d_truth, 0, P, dmax_xy_m=0.5, dmax_th_rad=np.deg2rad(20.0), seed=20261105)
+        eng.median_filter(d_scans); eng.sync()
+        scans = d_scans.cpu().numpy(); tr = d_truth.cpu().numpy()
+        rng = np.random.default_rng(7)
+        odo = tr + rng.normal(0, 1, (P, 3)) * [0.1, 0.1, np.deg2rad(3.0)]
+        grid = np.array([[dx, dy, np.deg2rad(dt)] for dx in (-0.3, 0.3) for dy in (-0.3, 0.3) for dt in (-10, -3.3, 3.3, 10)])
+        guess = (odo[:, None, :] + grid[None]).reshape(-1, 3)
+        ri = np.repeat(np.arange(P, dtype=np.int32) * 2, G); si = ri + 1
+        for cov in (0, 1):
+            p = eng.default_plicp_params()
+            p.do_compute_covariance = cov
+            one, a1, a2 = eng.plicp(scans, ri, si, first_guess=guess, params=p, want_corr=True)
+            ms, b1, b2 = eng.plicp(scans, ri, si, first_guess=guess, params=p, want_corr=True, multistart=True)
+            _same_records(ms, one, cov)
+            assert np.array_equal(a1, b1) and np.array_equal(a2, b2)   # every correspondence of every job
+        assert (one["valid"] == 1).mean() > 0.9 and (one["reserved"][:, 3] > 0).all()
+        # a broken promise: the second run of four mixes two pairs
+        ri2, si2 = ri.copy(), si.copy()
+        ri2[5], si2[5] = ri[G], si[G]
+        bad = eng.plicp(scans, ri2, si2, first_guess=guess, multistart=True)
+        assert bad["status"][5] == 4 and bad["valid"][5] == 0
+        keep = np.ones(P * G, bool); keep[5] = False
+        _same_records(bad[keep], one[keep], 0)   # (this call ran without the covariance)
+        # B not a multiple of 4: the flag is ignored, the single-job instance runs: the same bytes (covariance and diagnostics aside)
+        odd = eng.plicp(scans, ri[:-2], si[:-2], first_guess=guess[:-2], params=p, multistart=True)
+        odd = odd.copy(); odd["cov"] = one[:-2]["cov"]
+        odd["reserved"] = one[:-2]["reserved"]   # diagnostics (walks, steps): they follow the warps' timing on the list of unfinished walks
+        assert np.array_equal(odd.tobytes(), one[:-2].tobytes())
+    finally:
+        eng.close()
+    # short scans ignore the flag
+    g = load_log("fr079")
+    eng = zh.Engine(0)
+    try:
+        eng.set_laser(make_laser(g))
+        s = eng.median_filter(g["scans"][:41].copy())
+        r4 = np.repeat(np.arange(10, dtype=np.int32) * 4, 4)
+        a = eng.plicp(s, r4, r4 + 1)
+        b = eng.plicp(s, r4, r4 + 1, multistart=True)
+        assert np.array_equal(a.tobytes(), b.tobytes())
+    finally:
+        eng.close()
