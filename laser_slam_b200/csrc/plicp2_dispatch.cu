@@ -5,6 +5,7 @@
 #include "zhsm_internal.h"
 
 cudaError_t plicp_launch_t128(const PlicpArgs &a, cudaStream_t st);
+cudaError_t plicp_launch_t160(const PlicpArgs &a, cudaStream_t st);
 cudaError_t plicp_launch_t192(const PlicpArgs &a, cudaStream_t st);
 cudaError_t plicp_launch_t256(const PlicpArgs &a, cudaStream_t st);
 cudaError_t plicp_launch_t512(const PlicpArgs &a, cudaStream_t st);
@@ -21,7 +22,7 @@ cudaError_t plicp_launch_ms128(const PlicpArgs &a, cudaStream_t st);
 // guess 0, 4000 pairs: 256: 29.8 ms, 512 (1 CTA/SM): 36.6.
 void plicp_shape(int n, int knob_T, int *T, int *C, int *hash_chunk) {
     int t = n <= 640 ? 128 : n <= 1472 ? 192 : n <= 2304 ? 256 : 512;
-    if (knob_T == 128 || knob_T == 192 || knob_T == 256 || knob_T == 512) t = knob_T;
+    if (knob_T == 128 || knob_T == 160 || knob_T == 192 || knob_T == 256 || knob_T == 512) t = knob_T;
     while ((n + t - 1) / t > 32 && t < 512) t = t < 128 ? 128 : t < 256 ? 256 : 512;
     *T = t;
     *C = (n + t - 1) / t;
@@ -56,7 +57,7 @@ cudaError_t plicp_jump_launch(const PlicpArgs &a, short *jt, int32_t *owner, cud
 cudaError_t plicp_launch(const PlicpArgs &a, int sm_count, cudaStream_t st, int *launched) {
     (void)sm_count;
     const int T = a.T, C = (a.L.n + T - 1) / T;
-    if ((T != 128 && T != 192 && T != 256 && T != 512) || C > 32 || (a.hash_chunk & 1) || a.hash_chunk < C)
+    if ((T != 128 && T != 160 && T != 192 && T != 256 && T != 512) || C > 32 || (a.hash_chunk & 1) || a.hash_chunk < C)
         return cudaErrorInvalidValue;
     if (!a.jt || !a.owner) return cudaErrorInvalidValue;
     cudaError_t e = plicp_jump_launch(a, const_cast<short *>(a.jt), const_cast<int32_t *>(a.owner), st, launched);
@@ -67,7 +68,7 @@ cudaError_t plicp_launch(const PlicpArgs &a, int sm_count, cudaStream_t st, int 
         if (e == cudaSuccess && launched) *launched += 1;
         return e;
     }
-    e = T == 128 ? plicp_launch_t128(a, st) : T == 192 ? plicp_launch_t192(a, st) : T == 256 ? plicp_launch_t256(a, st) : plicp_launch_t512(a, st);
+    e = T == 128 ? plicp_launch_t128(a, st) : T == 160 ? plicp_launch_t160(a, st) : T == 192 ? plicp_launch_t192(a, st) : T == 256 ? plicp_launch_t256(a, st) : plicp_launch_t512(a, st);
     if (e == cudaSuccess && launched) *launched += 1;
     return e;
 }

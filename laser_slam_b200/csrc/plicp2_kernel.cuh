@@ -195,7 +195,7 @@ template <int T>
 __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const WalkCtx &w, const IterCtx &it, int C,
                                                          unsigned sens, bool chunked, const uint2 *jt_src,
                                                          const PendRef<kList<T>> &pr, WalkDiag &dg,
-                                                         PhaseClock &pc, JtPrefetch &tma STATS_PARAM) {
+                                                         PhaseClock &pc, JtPrefetch &tma, bool jt_in_place STATS_PARAM) {
     constexpr int NW = T / 32;
     const int t = pl_tid<T>(), lane = t & 31, warp = t >> 5;
     const int n = w.n;
@@ -208,7 +208,7 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
         if (tma.on) {
             // ... which a bulk copy issued after the previous select has already done (JtPrefetch): wait for its phase
             tma.wait();
-        } else {
+        } else if (!jt_in_place) {  // (else: copied behind the previous iteration's solve)
             uint2 *dst = PL_SH(uint2, l.jt);
             for (int q = t; q < n; q += T) dst[q] = __ldcs(jt_src + q);  // streaming: leave the L1 to the cs table
             pl_sync<T>();
@@ -324,14 +324,21 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
 #define PLICP_MINB_192 4   // resident CTAs per SM the 192-thread instance is compiled for (80 registers); tuning builds: 3
 #endif
 template <int T>
-__global__ void __launch_bounds__(T * PLICP_NS, (PLICP_NS > 1 ? 1 : T <= 192 ? PLICP_MINB_192 : T <= 288 ? 2 : 1))
-plicp2_kernel(PlicpArgs a) {
+__global__ void __launch_bounds__(T * PLICP_NS, (PLICP_NS > 1 ? 1 : T == 160 ? 5 : T <= 192 ? PLICP_MINB_192 : T <= 288 ? 2 : 1))
+plicp2_kernel(PlicpArgs a, const Lay lay0) {
     constexpr int NW = T / 32;
     const int n = a.L.n;
     const int C = (n + T - 1) / T;
     const int t = pl_tid<T>(), lane = t & 31, warp = t >> 5;
     const int job = PLICP_NS == 1 ? (int)blockIdx.x : (int)blockIdx.x * PLICP_NS + pl_slot<T>();
-    const Lay l = PLICP_NS == 1 ? make_layout(n, T) : make_layout_slots(n, T, PLICP_NS, pl_slot<T>());
+    // The shared-memory layout comes with the launch (plicp2_launch.cuh): its offsets are then operands from the
+    // constant bank instead of arithmetic on n that the compiler repeats wherever registers are short (4 % of the
+    // r02t capture's instructions).  lay0 is slot 0's layout; another slot's areas lie slot * slot_bytes further on.
+    Lay l = lay0;
+    if (PLICP_NS > 1) {
+        const unsigned d = slot_bytes(n, T) * (unsigned)pl_slot<T>();
+        l.d2j += d; l.red += d; l.ctl += d; l.hist += d; l.candi += d; l.cj1 += d; l.cj2 += d; l.spec += d;
+    }
     Ctl *ctl = PL_SH(Ctl, l.ctl);
     const LaserDev L = a.L;
     const zhsm_plicp_params &P = a.P;
@@ -448,6 +455,7 @@ plicp2_kernel(PlicpArgs a) {
     pc.mark(0);  // the block sums above were barriers: the tables are in place
 
     IterCtx it;
+    bool jt_in_place = false;  // the jump tables are in shared memory (they share it with the select's histograms)
     it.cs2 = a.cs;
     it.min_theta = (double)theta_f(L.fi_min, L.dfi, 0);
     it.C1 = (double)n / ((double)theta_f(L.fi_min, L.dfi, n - 1) - it.min_theta);
@@ -493,7 +501,7 @@ plicp2_kernel(PlicpArgs a) {
             it.cs = ctl->cs[par];
             it.sn = ctl->sn[par];
             if (t == 0) ctl->hash_acc[iteration & 1] = 0;
-            valid = find_correspondences<T>(l, wc, it, C, sens, iteration < a.chunk_iters, jt_src, pr, dg, pc, tma STATS_ARG);
+            valid = find_correspondences<T>(l, wc, it, C, sens, iteration < a.chunk_iters, jt_src, pr, dg, pc, tma, jt_in_place STATS_ARG);
             if (P.outliers_remove_doubles) {
                 for (int j = t; j < n; j += T) d2j[j] = BIG;  // the search used this area as its queue
                 pl_sync<T>();
@@ -634,12 +642,21 @@ plicp2_kernel(PlicpArgs a) {
             const int num_after = block_sum<T>(nkept, ctl->ired, 3);  // barrier: publishes red, cj1, cj2
             tma.issue();  // every thread is past the select: the histograms' area is free for the next search's tables
             pc.mark(6);
-            // ld_corr_hash of this iteration's correspondences, in parallel
-            {
-                unsigned hc = corr_hash_chunk(l, n, t, a.hash_chunk, a.hashmat);
+            // Warp 0 solves; the other warps, which would only wait for it, compute ld_corr_hash of this iteration's
+            // correspondences (T chunks over T - 32 threads) and bring the jump tables back for the next search (the
+            // select is done with the area they share; an iteration that turns out to be the last copies in vain).
+            if (warp != 0) {
+                unsigned hc = 0;
+#pragma unroll 1
+                for (int c = t - 32; c < T; c += T - 32) hc ^= corr_hash_chunk(l, n, c, a.hash_chunk, a.hashmat);
                 hc = __reduce_xor_sync(0xffffffffu, hc);
                 if (lane == 0 && hc) atomicXor(&ctl->hash_acc[iteration & 1], hc);
+                if (jt_src && !tma.on) {
+                    uint2 *dst = PL_SH(uint2, l.jt);
+                    for (int q = t - 32; q < n; q += T - 32) dst[q] = __ldcs(jt_src + q);
+                }
             }
+            jt_in_place = true;
             pc.mark(7);
             if (warp == 0) {
                 double v = 0;
@@ -752,7 +769,7 @@ plicp2_kernel(PlicpArgs a) {
         it.cs = ctl->cs[0];
         it.sn = ctl->sn[0];
         // "recompute correspondences in case of restarts" (icp.c): world coords at best x + tricks, no outlier pass
-        if (v_restarted) valid = find_correspondences<T>(l, wc, it, C, sens, a.chunk_iters > 0, jt_src, pr, dg, pc, tma STATS_ARG);
+        if (v_restarted) valid = find_correspondences<T>(l, wc, it, C, sens, a.chunk_iters > 0, jt_src, pr, dg, pc, tma, jt_in_place STATS_ARG);
     }
     tma.wait();  // a prefetch issued by the last iteration must have landed before the CTA gives up its shared memory
     if (t == 0) ctl->hash_acc[0] = 0;

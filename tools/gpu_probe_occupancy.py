@@ -29,6 +29,7 @@ r = res.cpu().numpy().view(zh.RESULT_DTYPE).reshape(-1)
 print("%%.2f ms (min of 3 after warm-up), hash-sum %%d" %% (min(ms[1:]), int(r["corr_hash"].astype(np.uint64).sum())))
 """ % ROOT
 for pad_kb in [int(v) for v in os.environ.get("PADS_KB", "0,20,58,150").split(",")]:
-    env = dict(os.environ, ZHSM_PLICP_SMEM_PAD=str(pad_kb * 1024))
+    env = dict(os.environ, ZHSM_PLICP_SMEM_PAD=str(pad_kb * 1024 + 1))   # odd: the launch reports its CTAs per SM
     out = subprocess.run([sys.executable, "-c", code, P, n], env=env, capture_output=True, text=True)
-    print(f"pad {pad_kb:3d} KB: {out.stdout.strip() or out.stderr.strip()[-300:]}")
+    occ = [ln for ln in out.stderr.splitlines() if "CTAs per SM" in ln][:1]
+    print(f"pad {pad_kb:3d} KB: {out.stdout.strip() or out.stderr.strip()[-300:]} {occ[0] if occ else ''}")
