@@ -342,7 +342,7 @@ extern "C" zhsm_status zhsm_plicp_batch(zhsm_handle *h, const float *scans, int 
     a.cs = h->d_cs;
     a.hashmat = h->d_hashmat;
     a.hash_chunk = h->hash_chunk;
-    a.chunk_iters = h->knob_chunk_iters;
+    a.chunk_iters = plicp_chunk_iters(h->knob_chunk_iters, h->hash_T);
     // ZHSM_MULTISTART: the caller promises jobs in runs of four that share both scans (pair-major multi-start).  Used
     // where it pays: long scans, whose single-job CTAs fit only twice per SM.  The kernel re-checks the promise per job.
     if ((flags & ZHSM_MULTISTART) && B % 4 == 0 && n > 1472 && plicp_ms128_smem_bytes(n) <= 227 * 1024 && (n + 127) / 128 <= 32 &&

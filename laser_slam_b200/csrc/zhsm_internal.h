@@ -27,7 +27,7 @@ struct zhsm_handle {
     // tuning knobs, read from the environment ONCE in zhsm_create (never on the launch path) and clamped
     int knob_T = 0;            // ZHSM_PLICP_T: 0 = by beam count, else 128 / 192 / 256 / 512
     int knob_chunk = 131072;   // ZHSM_PLICP_CHUNK: jobs per launch (bounds the jump-table scratch)
-    int knob_chunk_iters = 2;  // ZHSM_PLICP_CHUNK_ITERS: first iterations searched in chunk order
+    int knob_chunk_iters = -1; // ZHSM_PLICP_CHUNK_ITERS: first iterations searched in chunk order; -1: by CTA shape (plicp_chunk_iters)
     int knob_smem_pad = 0;     // ZHSM_PLICP_SMEM_PAD: extra dynamic shared memory (fewer CTAs per SM)
     int hash_T = 0, hash_C = 0;  // CTA shape the hash matrices were built for (zhsm_set_laser)
     uint32_t *d_hashmat_ms = nullptr;  // the same for the multi-start instance's shape (128 threads per job)
@@ -128,6 +128,11 @@ cudaError_t corridor_launch(const float *scans, const unsigned char *bad, const 
 zhsm_status zhsm_stage(zhsm_handle *h, int slot, size_t bytes, void **out);
 
 cudaError_t plicp_launch(const PlicpArgs &a, int sm_count, cudaStream_t st, int *launched);
+// First iterations of an icp_loop searched in chunk order (thread t walks rays [t*C, (t+1)*C) and hands last_best on:
+// fewer re-searched walks, lanes that wait for each other more).  Measured on one B200 (profiles/r02x_chunk_iters.txt):
+// 1080 beams, 192 threads: 0: 16.7+, 2: 16.33, 3: 16.29, 6: 16.56 ms per 20k pairs; 2048 beams, multi-start, 256
+// threads (long walks go to the list): 0: 87.3 k, 2: 84.4 k, 6: 77.1 k matches/s.
+inline int plicp_chunk_iters(int knob, int T) { return knob >= 0 ? knob : (T >= 256 ? 0 : 2); }
 size_t plicp_ms128_smem_bytes(int n);  // dynamic shared memory of the multi-start instance (4 jobs per CTA)
 size_t plicp_jump_bytes_per_job(int n);
 // CTA shape the PL-ICP kernel uses for n beams: T threads, C rays per thread, hash chunk (even) per thread
