@@ -74,6 +74,7 @@ struct Ctl {
     int npend;          // walks on the list of unfinished walks (plicp2_search.cuh)
     int pend_next;      // next list entry to be taken by a warp
     int steps_pend;     // walk steps of the walks that went through the list (finish_unfinished)
+    int work_next;      // next item of a round's pool of walks (plicp2_flat.cuh)
 };
 
 // byte offsets into the dynamic shared memory block

@@ -5,6 +5,7 @@
 #include "plicp2_common.cuh"
 #include "plicp2_cov.cuh"
 #include "plicp2_search.cuh"
+#include "plicp2_flat.cuh"
 #include "plicp2_select.cuh"
 #include "plicp2_solve.cuh"
 
@@ -17,6 +18,14 @@ namespace PL_NAMESPACE {
 #endif
 template <int T>
 constexpr bool kList = T >= PLICP_LIST_MIN_T;
+// ... and run a round's walks as one pool of work items (plicp2_flat.cuh) instead of one tricks_one call per ray
+#ifndef PLICP_FLAT
+#define PLICP_FLAT 1
+#endif
+template <int T>
+constexpr bool kFlat = kList<T> && PLICP_FLAT;
+// (The other instances keep their rays fixed per thread: drawing groups of 32 rays from the same counter measured
+// 16.38 against 16.34 ms per 20k pairs at 1080 beams and 11.80 against 11.60 ms per 40k pairs at 360 -- nothing.)
 
 // Per-phase cycle counters of thread 0 (tuning builds only: -DPLICP_PHASE_TIMING; the counters then REPLACE
 // x/cov/error/goodness/quality in the result record, see tools/gpu_probe_phases.py).
@@ -42,12 +51,6 @@ struct WalkDiag {
     int steps;  // walk steps this thread executed (probes of its walks: the budgets of tricks_one count them)
 };
 
-// pose of the current iteration + what make_ray needs
-struct IterCtx {
-    double x0, x1, cs, sn;
-    double min_theta, C1;
-    const double2 *cs2;  // (cos, sin) of the beam angles (handle table, global memory)
-};
 
 #ifdef PLICP_WALK_STATS
 // tuning build: per-thread walk statistics (trips, trips of walks > 32, count, trips of walks > 256, count, max)
@@ -214,7 +217,16 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
             pl_sync<T>();
         }
     }
-    if (!chunked) {
+    if (!chunked && kFlat<T>) {
+        if constexpr (kFlat<T>) {
+            if (t == 0) ctl->work_next = 0;
+            pl_sync<T>();
+            const BatchOut bo = walk_batch<T>(l, w, it, pr, n, false);
+            dg.walks += bo.walks;
+            dg.first += bo.walks;
+            dg.steps += bo.steps;
+        }
+    } else if (!chunked) {
 #pragma unroll 1
         for (int k = 0; k < C; k++)
             if (sens >> k & 1u) {
@@ -256,7 +268,7 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
     short *glast = queue + n;  // [C][NW]: j1 of the last ray with a correspondence in each group of 32 rays, or -1
     for (int round = 0;; round++) {
         int *qn = &ctl->qn[round & 1];
-        if (t == 0) ctl->qn[(round + 1) & 1] = 0;
+        if (t == 0) { ctl->qn[(round + 1) & 1] = 0; ctl->work_next = 0; }
 #pragma unroll 1
         for (int k = 0; k < C; k++) {
             const int i = k * T + t;
@@ -297,13 +309,21 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
         if (total == 0) break;
         dg.rounds++;
         int changed = 0, unfinished = 0;
+        if constexpr (kFlat<T>) {
+            const BatchOut bo = walk_batch<T>(l, w, it, pr, total, true);
+            changed = bo.flags & 1;
+            unfinished = bo.flags >> 1;
+            dg.walks += bo.walks;
+            dg.steps += bo.steps;
+        } else {
 #pragma unroll 1
-        for (int e = t; e < total; e += T) {
-            const int i = (int)queue[e];
-            const int before = cj1[i];
-            dg.walks++;
-            if (search_ray<kList<T>>(l, w, it, pr, i, dg.steps, pc STATS_ARG)) changed |= (int)cj1[i] != before;
-            else unfinished = 1;  // on the list: process_pending says whether its j1 changed
+            for (int e = t; e < total; e += T) {
+                const int i = (int)queue[e];
+                const int before = cj1[i];
+                dg.walks++;
+                if (search_ray<kList<T>>(l, w, it, pr, i, dg.steps, pc STATS_ARG)) changed |= (int)cj1[i] != before;
+                else unfinished = 1;  // on the list: process_pending says whether its j1 changed
+            }
         }
         // the usual end: nothing changed and nothing is unfinished -- last_best of every ray is what it was walked with
         if (!pl_sync_or<T>(changed | unfinished)) break;

@@ -48,6 +48,13 @@ __device__ __forceinline__ Ray make_ray(double2 p, double x0, double x1, double 
     return r;
 }
 
+// pose of the current iteration + what make_ray needs
+struct IterCtx {
+    double x0, x1, cs, sn;
+    double min_theta, C1;
+    const double2 *cs2;  // (cos, sin) of the beam angles (handle table, global memory)
+};
+
 // Geometry a walk needs besides the ray: 32-bit shared-window addresses of the ref tables and the beam angles.
 struct WalkCtx {
     unsigned refp, rr2, jt;  // shared-memory addresses (cvta.to.shared)
