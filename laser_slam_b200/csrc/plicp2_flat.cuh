@@ -14,6 +14,13 @@
 // occupancy the threshold keeps, prologue and epilogue run FLAT_R lanes or more at a time, and a warp that is done
 // early simply draws more of the pool: the round ends when the pool is empty, not when the unluckiest warp is done.
 //
+// Measured on one B200 (profiles/r02z_flat_variants_*.txt, r03a_variants*.txt; 65 536 multi-start jobs at 2048 beams /
+// 8 000 first-guess-0 pairs at 2048 beams): one tricks_one call per ray 85.5 k matches/s / 34.7 ms; the pool with
+// FLAT_R 8: 95.4 k / 29.8, 16: 97.6 k / 28.3, 24: 98.7 k / 27.6, 32 (a service trip only when nobody walks): 104.2 k /
+// 28.1 -- refilling inside a warp buys nothing over refilling the warp, the pool and the single loop do; list budgets
+// 112 / 64 probes: 104.6 k / 28.1, with the tail budget 16: 107.8 k / 26.7; 224 / 96 / 16: 113.0 k / 27.6 (chosen);
+// 448 / 192 / 16: 110.2 k / 30.6; without the list: 25.3 k / 168 ms.
+//
 // Decisions and operands are those of tricks_one, in the same order: the results are identical (the tests compare
 // the records of both paths bit for bit through the CTA-shape test).  Walks that outlive FLAT_LIST_* probes still go
 // to the list of unfinished walks and are finished warp-wide after the round (finish_unfinished): with the other
@@ -27,10 +34,13 @@ namespace PL_NAMESPACE {
 #define PLICP_FLAT_R 32
 #endif
 #ifndef PLICP_FLAT_LIST_BOTH
-#define PLICP_FLAT_LIST_BOTH 112   // probes after which a walk with both directions alive may go on the list
+#define PLICP_FLAT_LIST_BOTH 224   // probes after which a walk with both directions alive may go on the list
+#endif
+#ifndef PLICP_FLAT_TAIL
+#define PLICP_FLAT_TAIL 16         // ... once the round's pool is empty: what still walks then is the round's tail
 #endif
 #ifndef PLICP_FLAT_LIST_SOLO
-#define PLICP_FLAT_LIST_SOLO 64    // ... with one direction left
+#define PLICP_FLAT_LIST_SOLO 96    // ... with one direction left
 #endif
 
 struct BatchOut {
@@ -42,8 +52,8 @@ struct BatchOut {
 // Work items [0, total): item e is sens ray queue[e] (from_queue: a re-search round) or sens ray e itself (the first
 // pass; invalid sens rays are skipped).  ctl->work_next must be 0 and visible (a barrier) before the call; every
 // thread of the job calls.
-template <int T>
-static __device__ __noinline__ BatchOut walk_batch(const Lay l, const WalkCtx c, const IterCtx it, const PendRef<true> pr,
+template <int T, bool LIST>
+static __device__ __noinline__ BatchOut walk_batch(const Lay l, const WalkCtx c, const IterCtx it, const PendRef<LIST> pr,
                                                    int total, bool from_queue) {
     constexpr unsigned FULL = 0xffffffffu;
     const float HALF_PI_F = 1.57079632679489662f;
@@ -63,18 +73,21 @@ static __device__ __noinline__ BatchOut walk_batch(const Lay l, const WalkCtx c,
     // the lane's walk
     int state = 0;  // 0: no walk, 1: walking, 2: ended (epilogue pending)
     int ray_i = 0, j1 = -1, up = 0, down = 0, stopped = 0, probes = 0, start_cell = 0;
+    int limit = PLICP_FLAT_LIST_BOTH;  // probes after which this walk may go on the list
     double wx = 0, wy = 0, rho2 = 0, best = INFINITY, last_up = 0, last_down = 0;
     float phi = 0.f;
-    bool ask = true;   // may this walk still be put on the list?
+    bool ask = LIST;   // may this walk still be put on the list?
     bool more = true;  // (warp-uniform) the pool may still hold items
     BatchOut out;
     out.flags = 0; out.walks = 0; out.steps = 0;
 
 #pragma unroll 1
     for (;;) {
+        // lanes a service trip would serve: while the pool lasts every lane that is not walking, afterwards the
+        // lanes whose epilogue is pending (one ballot per trip until then)
         const unsigned m_walk = __ballot_sync(FULL, state == 1);
-        const unsigned m_end = __ballot_sync(FULL, state == 2);
-        const int want = __popc(m_end) + (more ? 32 - __popc(m_walk | m_end) : 0);
+        int want = 32 - __popc(m_walk);
+        if (!more) want = __popc(__ballot_sync(FULL, state == 2));
         if (m_walk == 0 && want == 0) break;
         if (want >= PLICP_FLAT_R || m_walk == 0) {
             // ---- service trip: epilogues, then new walks
@@ -106,13 +119,15 @@ static __device__ __noinline__ BatchOut walk_batch(const Lay l, const WalkCtx c,
                         up = we_start_at + 1; down = we_start_at;
                         last_up = 0; last_down = 0;
                         j1 = -1; best = INFINITY;
-                        stopped = 0; probes = 0; ask = true;
+                        stopped = 0; probes = 0; ask = LIST; limit = PLICP_FLAT_LIST_BOTH;
                         ray_i = i;
                         state = 1;
                         out.walks++;
                     }
                 }
             }
+            // the pool is empty: what still walks is the round's tail, and the list finishes long walks faster
+            if (!more) limit = limit < PLICP_FLAT_TAIL ? limit : PLICP_FLAT_TAIL;
             continue;
         }
         if (state != 1) continue;
@@ -157,8 +172,9 @@ static __device__ __noinline__ BatchOut walk_batch(const Lay l, const WalkCtx c,
                 down = now_up ? down : nidx;
             }
         }
+        if (stopped) limit = limit < PLICP_FLAT_LIST_SOLO ? limit : PLICP_FLAT_LIST_SOLO;
         if (stopped == 3) state = 2;
-        else if (ask && probes >= (stopped ? PLICP_FLAT_LIST_SOLO : PLICP_FLAT_LIST_BOTH)) {
+        else if (probes >= limit && ask) {
             WalkState st;
             st.best = best; st.i = ray_i; st.j1 = j1; st.pad_ = probes;
             if (stopped == 0) { st.last_up = last_up; st.last_down = last_down; st.up = up; st.down = down; st.dir = 2; }

@@ -22,8 +22,11 @@ constexpr bool kList = T >= PLICP_LIST_MIN_T;
 #ifndef PLICP_FLAT
 #define PLICP_FLAT 1
 #endif
+#ifndef PLICP_FLAT_ALL
+#define PLICP_FLAT_ALL 0   // tuning builds: the short-scan instances as well (no list there: every walk ends in its lane)
+#endif
 template <int T>
-constexpr bool kFlat = kList<T> && PLICP_FLAT;
+constexpr bool kFlat = PLICP_FLAT && (kList<T> || PLICP_FLAT_ALL);
 // (The other instances keep their rays fixed per thread: drawing groups of 32 rays from the same counter measured
 // 16.38 against 16.34 ms per 20k pairs at 1080 beams and 11.80 against 11.60 ms per 40k pairs at 360 -- nothing.)
 
@@ -221,7 +224,7 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
         if constexpr (kFlat<T>) {
             if (t == 0) ctl->work_next = 0;
             pl_sync<T>();
-            const BatchOut bo = walk_batch<T>(l, w, it, pr, n, false);
+            const BatchOut bo = walk_batch<T, kList<T>>(l, w, it, pr, n, false);
             dg.walks += bo.walks;
             dg.first += bo.walks;
             dg.steps += bo.steps;
@@ -310,7 +313,7 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
         dg.rounds++;
         int changed = 0, unfinished = 0;
         if constexpr (kFlat<T>) {
-            const BatchOut bo = walk_batch<T>(l, w, it, pr, total, true);
+            const BatchOut bo = walk_batch<T, kList<T>>(l, w, it, pr, total, true);
             changed = bo.flags & 1;
             unfinished = bo.flags >> 1;
             dg.walks += bo.walks;
