@@ -4,6 +4,7 @@
 
 #include "zhsm_internal.h"
 
+cudaError_t plicp_launch_t64(const PlicpArgs &a, cudaStream_t st);
 cudaError_t plicp_launch_t128(const PlicpArgs &a, cudaStream_t st);
 cudaError_t plicp_launch_t160(const PlicpArgs &a, cudaStream_t st);
 cudaError_t plicp_launch_t192(const PlicpArgs &a, cudaStream_t st);
@@ -20,10 +21,13 @@ cudaError_t plicp_launch_ms128(const PlicpArgs &a, cudaStream_t st);
 // knob_T (ZHSM_PLICP_T, read once in zhsm_create) overrides (tuning only).  Measured on one B200: 1080 beams, 20k pairs: 192 threads 16.8 ms, 256 (2
 // CTAs/SM) 23.9; 1440 beams, 10k pairs: 192: 21.4 ms, 256: 22.1; 1536 beams: 192: 24.3, 256: 22.7; 2048 beams, first
 // guess 0, 4000 pairs: 256: 29.8 ms, 512 (1 CTA/SM): 36.6.
+#ifndef PLICP_T64_MAX_BEAMS
+#define PLICP_T64_MAX_BEAMS 256
+#endif
 void plicp_shape(int n, int knob_T, int *T, int *C, int *hash_chunk) {
-    int t = n <= 640 ? 128 : n <= 1472 ? 192 : n <= 2304 ? 256 : 512;
-    if (knob_T == 128 || knob_T == 160 || knob_T == 192 || knob_T == 256 || knob_T == 512) t = knob_T;
-    while ((n + t - 1) / t > 32 && t < 512) t = t < 128 ? 128 : t < 256 ? 256 : 512;
+    int t = n <= PLICP_T64_MAX_BEAMS ? 64 : n <= 640 ? 128 : n <= 1472 ? 192 : n <= 2304 ? 256 : 512;
+    if (knob_T == 64 || knob_T == 128 || knob_T == 160 || knob_T == 192 || knob_T == 256 || knob_T == 512) t = knob_T;
+    while ((n + t - 1) / t > 32 && t < 512) t = t < 128 ? 128 : t < 256 ? 256 : 512;  // (a thread owns at most 32 rays)
     *T = t;
     *C = (n + t - 1) / t;
     int ch = (n + t - 1) / t;
@@ -57,7 +61,7 @@ cudaError_t plicp_jump_launch(const PlicpArgs &a, short *jt, int32_t *owner, cud
 cudaError_t plicp_launch(const PlicpArgs &a, int sm_count, cudaStream_t st, int *launched) {
     (void)sm_count;
     const int T = a.T, C = (a.L.n + T - 1) / T;
-    if ((T != 128 && T != 160 && T != 192 && T != 256 && T != 512) || C > 32 || (a.hash_chunk & 1) || a.hash_chunk < C)
+    if ((T != 64 && T != 128 && T != 160 && T != 192 && T != 256 && T != 512) || C > 32 || (a.hash_chunk & 1) || a.hash_chunk < C)
         return cudaErrorInvalidValue;
     if (!a.jt || !a.owner) return cudaErrorInvalidValue;
     cudaError_t e = plicp_jump_launch(a, const_cast<short *>(a.jt), const_cast<int32_t *>(a.owner), st, launched);
@@ -68,7 +72,7 @@ cudaError_t plicp_launch(const PlicpArgs &a, int sm_count, cudaStream_t st, int 
         if (e == cudaSuccess && launched) *launched += 1;
         return e;
     }
-    e = T == 128 ? plicp_launch_t128(a, st) : T == 160 ? plicp_launch_t160(a, st) : T == 192 ? plicp_launch_t192(a, st) : T == 256 ? plicp_launch_t256(a, st) : plicp_launch_t512(a, st);
+    e = T == 64 ? plicp_launch_t64(a, st) : T == 128 ? plicp_launch_t128(a, st) : T == 160 ? plicp_launch_t160(a, st) : T == 192 ? plicp_launch_t192(a, st) : T == 256 ? plicp_launch_t256(a, st) : plicp_launch_t512(a, st);
     if (e == cudaSuccess && launched) *launched += 1;
     return e;
 }

@@ -347,7 +347,7 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
 #define PLICP_MINB_192 4   // resident CTAs per SM the 192-thread instance is compiled for (80 registers); tuning builds: 3
 #endif
 template <int T>
-__global__ void __launch_bounds__(T * PLICP_NS, (PLICP_NS > 1 ? 1 : T == 160 ? 5 : T <= 192 ? PLICP_MINB_192 : T <= 288 ? 2 : 1))
+__global__ void __launch_bounds__(T * PLICP_NS, (PLICP_NS > 1 ? 1 : T == 64 ? 8 : T == 160 ? 5 : T <= 192 ? PLICP_MINB_192 : T <= 288 ? 2 : 1))
 plicp2_kernel(PlicpArgs a, const Lay lay0) {
     constexpr int NW = T / 32;
     const int n = a.L.n;

@@ -112,7 +112,7 @@ extern "C" zhsm_status zhsm_create(int device, zhsm_handle **out) {
         return ZHSM_ERR_CUDA;
     }
     // tuning knobs: read here once, clamped; the launch path never looks at the environment
-    if (const char *e = getenv("ZHSM_PLICP_T")) { int v = atoi(e); if (v == 128 || v == 160 || v == 192 || v == 256 || v == 512) h->knob_T = v; }
+    if (const char *e = getenv("ZHSM_PLICP_T")) { int v = atoi(e); if (v == 64 || v == 128 || v == 160 || v == 192 || v == 256 || v == 512) h->knob_T = v; }
     if (const char *e = getenv("ZHSM_PLICP_CHUNK")) { int v = atoi(e); if (v >= 1 && v <= (1 << 22)) h->knob_chunk = v; }
     if (const char *e = getenv("ZHSM_PLICP_CHUNK_ITERS")) { int v = atoi(e); if (v >= 0 && v <= ZHSM_MAX_ITER) h->knob_chunk_iters = v; }
     if (const char *e = getenv("ZHSM_PLICP_SMEM_PAD")) { int v = atoi(e); if (v >= 0 && v <= 160 * 1024) h->knob_smem_pad = (v & ~15) | (v & 1); }
