@@ -12,20 +12,25 @@ cudaError_t plicp_launch_t256(const PlicpArgs &a, cudaStream_t st);
 cudaError_t plicp_launch_t512(const PlicpArgs &a, cudaStream_t st);
 cudaError_t plicp_launch_ms128(const PlicpArgs &a, cudaStream_t st);
 
-// CTA size per beam count: as many resident CTAs per SM as the shared-memory footprint (~51 B per beam) and the
-// registers allow -- a job has serial stretches (the solve, the tail of a search round) that only other jobs on the
-// same SM can fill -- and then enough threads that a thread owns <= ~8 rays:
-//   n <= 640: 128 threads;  n <= 1472: 192 threads, 80 registers (4 CTAs/SM at 1080 beams, 3 up to 1472);
-//   n <= 2304: 256 threads, 128 registers, 2 CTAs/SM (2048 beams), the COOP instance whose long walks are finished
-//   warp-wide (plicp2_search.cuh);  else 512 threads (COOP as well).
-// knob_T (ZHSM_PLICP_T, read once in zhsm_create) overrides (tuning only).  Measured on one B200: 1080 beams, 20k pairs: 192 threads 16.8 ms, 256 (2
-// CTAs/SM) 23.9; 1440 beams, 10k pairs: 192: 21.4 ms, 256: 22.1; 1536 beams: 192: 24.3, 256: 22.7; 2048 beams, first
-// guess 0, 4000 pairs: 256: 29.8 ms, 512 (1 CTA/SM): 36.6.
+// CTA size per beam count.  What counts is jobs per SM (the shared-memory footprint, ~51 B per beam, decides: 4 at 1080
+// beams) and then registers per thread, not warps per SM: a job has serial stretches that only other jobs on the same
+// SM can fill, and threads beyond ~8 rays each mostly wait at the job's barriers.
+//   n <= 400: 64 threads, 128 registers, 8 CTAs/SM;   n <= 1000: 128 threads, 128 registers, 4 CTAs/SM;
+//   n <= 1472: 192 threads, 80 registers (4 CTAs/SM at 1080 beams, 3 up to 1472);
+//   n <= 2304: 256 threads, 128 registers, 2 CTAs/SM (2048 beams), whose walks run as a pool and whose long walks
+//   are finished warp-wide (plicp2_flat.cuh, plicp2_search.cuh);  else 512 threads (the same).
+// knob_T (ZHSM_PLICP_T, read once in zhsm_create) overrides (tuning only).  Measured on one B200, ms per call
+// (profiles/r03c_cta_shapes.txt), threads 64 / 128 / 192 / 256:
+//   181 beams, 80k pairs: 21.0 / 24.7;  256, 80k: 16.8 / 19.9;  361, 60k: 16.1 / 17.6;  400, 40k: 11.7 / 13.0;
+//   480, 40k: 14.1 / 14.2 / 15.3;  640, 40k: 20.2 / 17.8 / 19.3;  800, 40k: 26.4 / 22.8 / 23.6;  880, 20k: - / 12.4 / 12.8;
+//   1000, 20k: - / 14.8 / 15.3;  1080, 20k: - / 16.33 / 16.34;  1200, 10k: - / - / 14.2 / 15.3;
+//   1440, 10k: - / 20.7 / 19.6 / 19.5;  2048 beams, first guess 0, 8000 pairs: 256: 27.6, 512 (1 CTA/SM): slower.
+// (Five 128-thread CTAs at 96 registers where the footprint allows, n <= 880: 3 % faster there, 5 % slower above.)
 #ifndef PLICP_T64_MAX_BEAMS
-#define PLICP_T64_MAX_BEAMS 256
+#define PLICP_T64_MAX_BEAMS 400
 #endif
 void plicp_shape(int n, int knob_T, int *T, int *C, int *hash_chunk) {
-    int t = n <= PLICP_T64_MAX_BEAMS ? 64 : n <= 640 ? 128 : n <= 1472 ? 192 : n <= 2304 ? 256 : 512;
+    int t = n <= PLICP_T64_MAX_BEAMS ? 64 : n <= 1000 ? 128 : n <= 1472 ? 192 : n <= 2304 ? 256 : 512;
     if (knob_T == 64 || knob_T == 128 || knob_T == 160 || knob_T == 192 || knob_T == 256 || knob_T == 512) t = knob_T;
     while ((n + t - 1) / t > 32 && t < 512) t = t < 128 ? 128 : t < 256 ? 256 : 512;  // (a thread owns at most 32 rays)
     *T = t;

@@ -173,7 +173,7 @@ def test_plicp_degenerate_distances(engine):
     assert np.abs(res["x"][same]).max() < 1e-9
 
 
-@pytest.mark.parametrize("threads", [128, 192, 256, 512])
+@pytest.mark.parametrize("threads", [64, 128, 160, 192, 256, 512])
 def test_plicp_independent_of_cta_shape(threads):
     """The CTA size (plicp_shape; ZHSM_PLICP_T is its tuning override) changes which thread owns which ray, the order
     of the floating-point block sums, the chunks of the first iterations and of the parallel hash -- never the
