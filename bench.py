@@ -32,8 +32,8 @@ MAX_RANGE_CM = 3000
 SEED = 20261104
 # dram__bytes_read.sum + dram__bytes_write.sum of one plicp2_kernel<192> launch over 20 000 pairs, from the committed
 # capture named here (tools/ncu_summary.py prints both numbers)
-NCU_DRAM_CAPTURE = "profiles/r02t_plicp2_T192_raw_metrics.txt"
-NCU_DRAM_BYTES_PER_PAIR = (349.910016e6 + 31.678720e6) / 20000
+NCU_DRAM_CAPTURE = "profiles/r03f_plicp2_T192_raw_metrics.txt"
+NCU_DRAM_BYTES_PER_PAIR = (352.156416e6 + 43.235840e6) / 20000
 
 
 def make_laser(zh):

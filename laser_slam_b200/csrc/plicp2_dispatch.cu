@@ -15,7 +15,7 @@ cudaError_t plicp_launch_ms128(const PlicpArgs &a, cudaStream_t st);
 // CTA size per beam count.  What counts is jobs per SM (the shared-memory footprint, ~51 B per beam, decides: 4 at 1080
 // beams) and then registers per thread, not warps per SM: a job has serial stretches that only other jobs on the same
 // SM can fill, and threads beyond ~8 rays each mostly wait at the job's barriers.
-//   n <= 400: 64 threads, 128 registers, 8 CTAs/SM;   n <= 1000: 128 threads, 128 registers, 4 CTAs/SM;
+//   n <= 1000: 128 threads, 128 registers, 4 CTAs/SM;
 //   n <= 1472: 192 threads, 80 registers (4 CTAs/SM at 1080 beams, 3 up to 1472);
 //   n <= 2304: 256 threads, 128 registers, 2 CTAs/SM (2048 beams), whose walks run as a pool and whose long walks
 //   are finished warp-wide (plicp2_flat.cuh, plicp2_search.cuh);  else 512 threads (the same).
@@ -26,8 +26,14 @@ cudaError_t plicp_launch_ms128(const PlicpArgs &a, cudaStream_t st);
 //   1000, 20k: - / 14.8 / 15.3;  1080, 20k: - / 16.33 / 16.34;  1200, 10k: - / - / 14.2 / 15.3;
 //   1440, 10k: - / 20.7 / 19.6 / 19.5;  2048 beams, first guess 0, 8000 pairs: 256: 27.6, 512 (1 CTA/SM): slower.
 // (Five 128-thread CTAs at 96 registers where the footprint allows, n <= 880: 3 % faster there, 5 % slower above.)
+// The 64-thread instance (8 CTAs/SM) wins every UNIFORM batch up to 400 beams above by 9-19 % -- and loses on the real
+// logs, whose jobs differ by an order of magnitude (sm_icp restarts on 10 % of intel-lab's pairs, 3.4-4 loops per pair
+// on fr079 / mit-cscail): log x 16 in one batch, k pairs/s, threads 64 / 128 / 192: intel-lab (181 beams) 921 / 970 /
+// 966, fr079 (361) 242 / 306 / 291, mit-cscail (361) 195 / 254 / 241; the log once: 380 / 454 / 472, 109 / 144 / 150,
+// 58 / 85 / 86 (profiles/r03d_logs_by_threads.txt).  A long job wants its threads; the instance stays selectable
+// (ZHSM_PLICP_T=64), off.
 #ifndef PLICP_T64_MAX_BEAMS
-#define PLICP_T64_MAX_BEAMS 400
+#define PLICP_T64_MAX_BEAMS 0   // (off: see above)
 #endif
 void plicp_shape(int n, int knob_T, int *T, int *C, int *hash_chunk) {
     int t = n <= PLICP_T64_MAX_BEAMS ? 64 : n <= 1000 ? 128 : n <= 1472 ? 192 : n <= 2304 ? 256 : 512;

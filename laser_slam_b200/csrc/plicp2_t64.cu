@@ -1,5 +1,6 @@
-// laser_slam_b200/csrc/plicp2_t64.cu -- PL-ICP kernel instance with 64-thread CTAs (one CTA per scan pair): scans of up
-// to 400 beams (the 181- and 361-beam SICK logs), eight resident CTAs per SM at 128 registers.
+// laser_slam_b200/csrc/plicp2_t64.cu -- PL-ICP kernel instance with 64-thread CTAs (one CTA per scan pair): eight
+// resident CTAs per SM at 128 registers.  Tuning only (ZHSM_PLICP_T=64): faster on uniform batches of short scans, slower
+// on the real logs (plicp2_dispatch.cu).
 #include "plicp2_kernel.cuh"
 #include "plicp2_launch.cuh"
 

@@ -14,6 +14,16 @@ if os.environ.get("ZHSM_PROBE_C5", "0") != "0":   # the 2048-beam multi-start wo
     import c5_workload
     eng, scans, ri, si, guess = c5_workload.make(zh, P // 16)
     P = ri.numel()
+elif os.environ.get("ZHSM_PROBE_LOG"):               # a CARMEN log x 16 (consecutive-scan odometry, first guess 0)
+    from tests.support import load_log, make_laser
+    g = load_log(os.environ["ZHSM_PROBE_LOG"])
+    eng = zh.Engine(0); eng.set_laser(make_laser(g))
+    dev = torch.device("cuda:0")
+    raw = np.ascontiguousarray(g["scans"]); S = raw.shape[0]
+    scans = torch.from_numpy(raw).to(dev).repeat(16, 1); eng.median_filter(scans)
+    ri = torch.cat([torch.arange(0, S - 1, dtype=torch.int32, device=dev) + k * S for k in range(16)]); si = ri + 1
+    guess = None
+    P = ri.numel()
 else:
     eng = zh.Engine(0); eng.set_laser(bench.make_laser(zh))
     dev = torch.device("cuda:0")
