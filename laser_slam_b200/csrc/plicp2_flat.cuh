@@ -14,15 +14,16 @@
 // occupancy the threshold keeps, prologue and epilogue run FLAT_R lanes or more at a time, and a warp that is done
 // early simply draws more of the pool: the round ends when the pool is empty, not when the unluckiest warp is done.
 //
-// Measured on one B200 (profiles/r02z_flat_variants_*.txt, r03a_variants*.txt; 65 536 multi-start jobs at 2048 beams /
+// Measured on one B200 (profiles/r02z_flat_variants_*.txt, r03a_flat_tail_variants_*.txt; 65 536 multi-start jobs at 2048 beams /
 // 8 000 first-guess-0 pairs at 2048 beams): one tricks_one call per ray 85.5 k matches/s / 34.7 ms; the pool with
 // FLAT_R 8: 95.4 k / 29.8, 16: 97.6 k / 28.3, 24: 98.7 k / 27.6, 32 (a service trip only when nobody walks): 104.2 k /
 // 28.1 -- refilling inside a warp buys nothing over refilling the warp, the pool and the single loop do; list budgets
 // 112 / 64 probes: 104.6 k / 28.1, with the tail budget 16: 107.8 k / 26.7; 224 / 96 / 16: 113.0 k / 27.6 (chosen);
 // 448 / 192 / 16: 110.2 k / 30.6; without the list: 25.3 k / 168 ms.
 //
-// Decisions and operands are those of tricks_one, in the same order: the results are identical (the tests compare
-// the records of both paths bit for bit through the CTA-shape test).  Walks that outlive FLAT_LIST_* probes still go
+// Decisions and operands are those of tricks_one, in the same order: the results are identical (the digest of
+// tools/gpu_probe_c5.py over 65 536 jobs did not move; tests/test_plicp_gpu.py compares this path with the oracle on
+// 2048-beam jobs with poor first guesses and, through the CTA-shape test, on a log).  Walks that outlive FLAT_LIST_* probes still go
 // to the list of unfinished walks and are finished warp-wide after the round (finish_unfinished): with the other
 // lanes kept busy they no longer cost lanes, only the round's tail.
 #pragma once
@@ -31,7 +32,7 @@
 namespace PL_NAMESPACE {
 
 #ifndef PLICP_FLAT_R
-#define PLICP_FLAT_R 32
+#define PLICP_FLAT_R 32            // lanes without a walk that trigger a service trip (32: only when no lane walks)
 #endif
 #ifndef PLICP_FLAT_LIST_BOTH
 #define PLICP_FLAT_LIST_BOTH 224   // probes after which a walk with both directions alive may go on the list
