@@ -115,6 +115,7 @@ extern "C" zhsm_status zhsm_create(int device, zhsm_handle **out) {
     if (const char *e = getenv("ZHSM_PLICP_T")) { int v = atoi(e); if (v == 64 || v == 128 || v == 160 || v == 192 || v == 256 || v == 512) h->knob_T = v; }
     if (const char *e = getenv("ZHSM_PLICP_CHUNK")) { int v = atoi(e); if (v >= 1 && v <= (1 << 22)) h->knob_chunk = v; }
     if (const char *e = getenv("ZHSM_PLICP_CHUNK_ITERS")) { int v = atoi(e); if (v >= 0 && v <= ZHSM_MAX_ITER) h->knob_chunk_iters = v; }
+    if (const char *e = getenv("ZHSM_PLICP_POOL")) h->knob_pool = atoi(e) != 0;
     if (const char *e = getenv("ZHSM_PLICP_SMEM_PAD")) { int v = atoi(e); if (v >= 0 && v <= 160 * 1024) h->knob_smem_pad = (v & ~15) | (v & 1); }
     *out = h;
     return ZHSM_OK;
@@ -343,6 +344,7 @@ extern "C" zhsm_status zhsm_plicp_batch(zhsm_handle *h, const float *scans, int 
     a.hashmat = h->d_hashmat;
     a.hash_chunk = h->hash_chunk;
     a.chunk_iters = plicp_chunk_iters(h->knob_chunk_iters, h->hash_T);
+    a.pool = h->knob_pool;
     // ZHSM_MULTISTART: the caller promises jobs in runs of four that share both scans (pair-major multi-start).  Used
     // where it pays: long scans, whose single-job CTAs fit only twice per SM.  The kernel re-checks the promise per job.
     if ((flags & ZHSM_MULTISTART) && B % 4 == 0 && n > 1472 && plicp_ms128_smem_bytes(n) <= 227 * 1024 && (n + 127) / 128 <= 32 &&

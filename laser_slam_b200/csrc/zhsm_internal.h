@@ -29,6 +29,7 @@ struct zhsm_handle {
     int knob_chunk = 131072;   // ZHSM_PLICP_CHUNK: jobs per launch (bounds the jump-table scratch)
     int knob_chunk_iters = -1; // ZHSM_PLICP_CHUNK_ITERS: first iterations searched in chunk order; -1: by CTA shape (plicp_chunk_iters)
     int knob_smem_pad = 0;     // ZHSM_PLICP_SMEM_PAD: extra dynamic shared memory (fewer CTAs per SM)
+    int knob_pool = 1;         // ZHSM_PLICP_POOL=0: the 256-thread shape runs its instance without the walk pool (plicp2_t256r.cu; tests)
     int hash_T = 0, hash_C = 0;  // CTA shape the hash matrices were built for (zhsm_set_laser)
     uint32_t *d_hashmat_ms = nullptr;  // the same for the multi-start instance's shape (128 threads per job)
     int hash_chunk_ms = 0;
@@ -87,6 +88,7 @@ struct PlicpArgs {
     const uint32_t *hashmat; // [T][32] GF(2) matrices of the parallel ld_corr_hash (plicp2_select.cuh)
     int hash_chunk;          // stream elements hashed per thread (even)
     int chunk_iters;         // first iterations of an icp_loop searched in chunk order (find_correspondences)
+    int pool;                // 0: the 256-thread shape is launched from plicp2_t256r.cu (no walk pool); tests only
     int B;
     LaserDev L;
     zhsm_plicp_params P;

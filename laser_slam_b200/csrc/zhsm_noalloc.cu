@@ -104,6 +104,7 @@ extern "C" zhsm_status zhsm_plicp_batch_noalloc(zhsm_handle *h, const float *d_s
     a.hashmat = h->d_hashmat;
     a.hash_chunk = h->hash_chunk;
     a.chunk_iters = plicp_chunk_iters(h->knob_chunk_iters, h->hash_T);
+    a.pool = h->knob_pool;
     a.scans = d_scans;
     a.ref_idx = d_ref_idx;
     a.sens_idx = d_sens_idx;

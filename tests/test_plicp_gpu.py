@@ -324,6 +324,60 @@ def test_engine_rejects_malformed_device_tensors():
     eng.close()
 
 
+def test_walk_pool_same_bytes_as_ray_by_ray():
+    """The long-scan instances run a round's walks as one pool behind a shared counter (plicp2_flat.cuh); ZHSM_PLICP_POOL=0
+    (read in zhsm_create, tests only) launches the 256-thread shape from an instance built without the pool
+    (plicp2_t256r.cu), which calls tricks_one ray by ray as the short-scan instances do.  Same
+    decisions on the same operands: the records (diagnostics aside) and every correspondence must be the same BYTES, on
+    2048-beam multi-start jobs with poor first guesses (pool, tail budget and the list of unfinished walks all busy) and
+    with the covariance on."""
+    import os
+    import torch
+    import laser_slam_b200 as zh
+    P, G, n = 32, 16, 2048
+    PM_PI = 3.141592654
+    lz = zh.Laser()
+    lz.n = n; lz.fi_min = np.float32(-PM_PI); lz.dfi = np.float32((360 * PM_PI / 180) / (n - 1.0))
+    lz.min_range_cm = 10; lz.max_range_cm = 3000; lz.min_valid_points = n // 5; lz.scan_window = n // 10
+    out = {}
+    old = os.environ.get("ZHSM_PLICP_POOL")
+    try:
+        for pool in ("1", "0"):
+            os.environ["ZHSM_PLICP_POOL"] = pool
+            eng = zh.Engine(0)
+            try:
+                eng.set_laser(lz)
+                dev = torch.device("cuda:0")
+                d_scans = torch.empty((2 * P, n), dtype=torch.float32, device=dev)
+                d_truth = torch.empty((P, 3), dtype=torch.float64, device=dev)
+                eng.synth_pairs(d_scans, d_truth, 0, P, dmax_xy_m=0.5, dmax_th_rad=np.deg2rad(20.0), seed=20261106)
+                eng.median_filter(d_scans); eng.sync()
+                scans = d_scans.cpu().numpy(); tr = d_truth.cpu().numpy()
+                rng = np.random.default_rng(11)
+                odo = tr + rng.normal(0, 1, (P, 3)) * [0.1, 0.1, np.deg2rad(3.0)]
+                grid = np.array([[dx, dy, np.deg2rad(dt)] for dx in (-0.3, 0.3) for dy in (-0.3, 0.3) for dt in (-10, -3.3, 3.3, 10)])
+                guess = (odo[:, None, :] + grid[None]).reshape(-1, 3)
+                ri = np.repeat(np.arange(P, dtype=np.int32) * 2, G); si = ri + 1
+                p = eng.default_plicp_params()
+                p.do_compute_covariance = 1
+                out[pool] = eng.plicp(scans, ri, si, first_guess=guess, params=p, want_corr=True)
+            finally:
+                eng.close()
+    finally:
+        if old is None:
+            os.environ.pop("ZHSM_PLICP_POOL", None)
+        else:
+            os.environ["ZHSM_PLICP_POOL"] = old
+    (a, a1, a2), (b, b1, b2) = out["1"], out["0"]
+    assert (a["valid"] == 1).mean() > 0.9
+    assert (a["reserved"][:, 3] != b["reserved"][:, 3]).any()     # the two paths really differ (their step counts do)
+    assert np.array_equal(a1, b1) and np.array_equal(a2, b2)
+    a, b = a.copy(), b.copy()
+    assert np.allclose(a["cov"], b["cov"], rtol=1e-6, atol=1e-15)  # (shared-memory atomics)
+    a["cov"] = b["cov"]; a["reserved"] = b["reserved"]
+    assert np.array_equal(a.tobytes(), b.tobytes())
+
+
 def _same_records(a, b, with_cov):
     """Two CTA shapes of the kernel on the same jobs: every integer of the record equal (valid, status, iterations, nvalid,
     correspondence hash, loops), pose and error equal to rounding (the 14 GPC sums are added in a tree whose shape follows
