@@ -220,15 +220,15 @@ __device__ __forceinline__ unsigned find_correspondences(const Lay &l, const Wal
             pl_sync<T>();
         }
     }
-    if (!chunked && kFlat<T>) {
-        if constexpr (kFlat<T>) {
-            if (t == 0) ctl->work_next = 0;
-            pl_sync<T>();
-            const BatchOut bo = walk_batch<T, kList<T>>(l, w, it, pr, n, false);
-            dg.walks += bo.walks;
-            dg.first += bo.walks;
-            dg.steps += bo.steps;
-        }
+    if constexpr (kFlat<T>) {
+        // the pool instances have no chunk-order iterations (they lose there: plicp_chunk_iters), so the ray-by-ray
+        // search is not compiled into them at all
+        if (t == 0) ctl->work_next = 0;
+        pl_sync<T>();
+        const BatchOut bo = walk_batch<T, kList<T>>(l, w, it, pr, n, false);
+        dg.walks += bo.walks;
+        dg.first += bo.walks;
+        dg.steps += bo.steps;
     } else if (!chunked) {
 #pragma unroll 1
         for (int k = 0; k < C; k++)

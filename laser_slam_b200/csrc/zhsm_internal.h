@@ -134,6 +134,7 @@ cudaError_t plicp_launch(const PlicpArgs &a, int sm_count, cudaStream_t st, int 
 // fewer re-searched walks, lanes that wait for each other more).  Measured on one B200 (profiles/r02x_chunk_iters.txt):
 // 1080 beams, 192 threads: 0: 16.7+, 2: 16.33, 3: 16.29, 6: 16.56 ms per 20k pairs; 2048 beams, multi-start, 256
 // threads (long walks go to the list): 0: 87.3 k, 2: 84.4 k, 6: 77.1 k matches/s.
+// (the instances that run their walks as a pool, T >= 256, ignore the value: they have no chunk order)
 inline int plicp_chunk_iters(int knob, int T) { return knob >= 0 ? knob : (T >= 256 ? 0 : 2); }
 size_t plicp_ms128_smem_bytes(int n);  // dynamic shared memory of the multi-start instance (4 jobs per CTA)
 size_t plicp_jump_bytes_per_job(int n);
