@@ -390,12 +390,13 @@ plicp2_kernel(PlicpArgs a, const Lay lay0) {
     }
     if (bad_job) {
         // device-resident job lists are not checked by the host: a bad index fails its own job, never the batch
+        const int ob = a.out_idx ? a.out_idx[job] : job;
         if (t == 0) {
             zhsm_result r = {};
             r.status = ZHSM_JOB_INVALID_SCAN;
-            a.results[job] = r;
+            a.results[ob] = r;
         }
-        if (a.corr_j1) for (int i = t; i < n; i += T) { a.corr_j1[(size_t)job * n + i] = -1; a.corr_j2[(size_t)job * n + i] = -1; }
+        if (a.corr_j1) for (int i = t; i < n; i += T) { a.corr_j1[(size_t)ob * n + i] = -1; a.corr_j2[(size_t)ob * n + i] = -1; }
         if (PLICP_NS > 1 && t == 0) atomicAdd((int *)&msctl[0], 1);  // this slot never reads the shared arrays
         return;
     }
@@ -457,9 +458,10 @@ plicp2_kernel(PlicpArgs a, const Lay lay0) {
     const int tot = block_sum<T>((nvf_ref << 16) | nvf_sens, ctl->ired, 0);
     const int tot_bad = pl_sync_or<T>(bad_field);
     const int tot_ref = tot >> 16, tot_sens = tot & 0xffff;
-    zhsm_result *res = a.results + job;
-    int16_t *oj1 = a.corr_j1 ? a.corr_j1 + (size_t)job * n : nullptr;
-    int16_t *oj2 = a.corr_j2 ? a.corr_j2 + (size_t)job * n : nullptr;
+    const int out = a.out_idx ? a.out_idx[job] : job;
+    zhsm_result *res = a.results + out;
+    int16_t *oj1 = a.corr_j1 ? a.corr_j1 + (size_t)out * n : nullptr;
+    int16_t *oj2 = a.corr_j2 ? a.corr_j2 + (size_t)out * n : nullptr;
     const bool guess_nan = isnan(ctl->x[0][0]) || isnan(ctl->x[0][1]) || isnan(ctl->x[0][2]);
     const bool fields_bad = tot_bad || tot_ref < n * 0.10 || tot_sens < n * 0.10;
     if (fields_bad || guess_nan) {
@@ -514,8 +516,26 @@ plicp2_kernel(PlicpArgs a, const Lay lay0) {
     int *st_ = st_arr;
 #endif
 
+    if (a.fin) {
+        // The last pass of a job whose restarts ran as a second batch (zhsm_api.cu: plicp_fanout): the bookkeeping of
+        // sm_icp comes with the launch, what is left is "recompute correspondences in case of restarts" and the record.
+        if (t == 0) {
+            const PlicpFin f = a.fin[job];
+            for (int k = 0; k < 3; k++) best_x[k] = f.x[k];
+            best_error = f.error;
+            nvalid0 = f.nvalid;
+            iterations = f.iterations;
+            n_loops = f.n_loops;
+            valid_out = 1;
+            restarted = 1;
+            dg.walks += f.diag[0]; dg.first += f.diag[1]; dg.rounds += f.diag[2]; dg.steps += f.diag[3];
+            ctl->fin = 1 | 2;
+        }
+        pl_sync<T>();
+    }
     // (the compiler unrolls this loop of 7: 600 KB of code, and 3.4 % FASTER on the 1080-beam batch than with
     // `#pragma unroll 1` -- the first copy, the only one most jobs run, is specialised for loop == 0; measured r02p)
+    if (!a.fin)
     for (int loop = 0; loop < 7; loop++) {
         int iteration = 0, all_ok = 1, par = 0, newest = 0;
         for (iteration = 0; iteration < max_it; iteration++) {

@@ -116,6 +116,7 @@ extern "C" zhsm_status zhsm_create(int device, zhsm_handle **out) {
     if (const char *e = getenv("ZHSM_PLICP_CHUNK")) { int v = atoi(e); if (v >= 1 && v <= (1 << 22)) h->knob_chunk = v; }
     if (const char *e = getenv("ZHSM_PLICP_CHUNK_ITERS")) { int v = atoi(e); if (v >= 0 && v <= ZHSM_MAX_ITER) h->knob_chunk_iters = v; }
     if (const char *e = getenv("ZHSM_PLICP_POOL")) h->knob_pool = atoi(e) != 0;
+    if (const char *e = getenv("ZHSM_PLICP_FANOUT")) { int v = atoi(e); if (v >= 0) h->knob_fanout = v; }
     if (const char *e = getenv("ZHSM_PLICP_SMEM_PAD")) { int v = atoi(e); if (v >= 0 && v <= 160 * 1024) h->knob_smem_pad = (v & ~15) | (v & 1); }
     *out = h;
     return ZHSM_OK;
@@ -304,6 +305,142 @@ extern "C" zhsm_status zhsm_median_filter_batch(zhsm_handle *h, float *scans, in
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// sm_icp's restart loop as a second batch (plicp_fanout)
+// ---------------------------------------------------------------------------------------------------------
+// sm_icp (CSM icp.c) restarts a match whose mean error is above restart_threshold_mean_error from six
+// perturbed poses, one icp_loop after the other, and keeps the best.  Each of those loops depends on its start pose
+// only, so a SMALL batch -- a log run once, the batch of one behind the CSM-shaped sm_icp() -- need not wait for its
+// few seven-loop jobs: pass A runs every job with restarts off (one icp_loop each), the jobs that sm_icp would restart
+// are listed, pass B runs their 6 R perturbed loops as ordinary one-loop jobs, a small kernel does sm_icp's
+// bookkeeping (the first failing restart ends the loop, strict < keeps the earliest best, iterations add up), and
+// pass C -- the PL-ICP kernel in its final-only mode (PlicpArgs::fin) -- recomputes the correspondences at the best
+// pose and writes the record.  Same records as the in-job restart loop (tests/test_plicp_gpu.py compares the bytes).
+// Large batches keep the in-job loop: there the long jobs are a matter of throughput, which is the same either way.
+// (also takes the listed jobs' scan indices along: after the host has read the count, nothing reads the caller's job
+// arrays any more -- with ZHSM_JOBS_ON_DEVICE they are only promised to live as long as an ordinary pass needs them)
+static __global__ void restart_select_kernel(const zhsm_result *res, const int32_t *ref_idx, const int32_t *sens_idx, int B,
+                                             double threshold, int32_t *list, int32_t *ref_f, int32_t *sens_f, int32_t *count) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= B) return;
+    const zhsm_result r = res[j];
+    // icp.c: restart && (best_error / nvalid) > restart_threshold_mean_error, after a valid first loop
+    if (r.valid == 1 && (r.error / r.nvalid) > threshold) {
+        const int slot = atomicAdd(count, 1);
+        list[slot] = j;
+        ref_f[slot] = ref_idx[j];
+        sens_f[slot] = sens_idx[j];
+    }
+}
+
+static __global__ void restart_jobs_kernel(const zhsm_result *res, const int32_t *ref_f, const int32_t *sens_f,
+                                           const int32_t *list, int R, double dt, double dth, int32_t *ref_b,
+                                           int32_t *sens_b, double *guess_b) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= 6 * R) return;
+    const int j = list[s / 6], k = s % 6;
+    ref_b[s] = ref_f[s / 6];
+    sens_b[s] = sens_f[s / 6];
+    // icp.c's perturbations in its order: +-dt in x, +-dt in y, +-dtheta
+    const double pert[6][3] = {{dt, 0, 0}, {-dt, 0, 0}, {0, dt, 0}, {0, -dt, 0}, {0, 0, dth}, {0, 0, -dth}};
+    for (int q = 0; q < 3; q++) guess_b[3 * (size_t)s + q] = res[j].x[q] + pert[k][q];
+}
+
+static __global__ void restart_combine_kernel(const zhsm_result *res, const zhsm_result *res_b, const int32_t *list, int R,
+                                              PlicpFin *fin) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= R) return;
+    const int j = list[r];
+    const zhsm_result a = res[j];
+    PlicpFin f;
+    for (int q = 0; q < 3; q++) f.x[q] = a.x[q];
+    f.error = a.error;
+    f.nvalid = a.nvalid;
+    f.iterations = a.iterations;
+    f.n_loops = 1;
+    for (int q = 0; q < 4; q++) f.diag[q] = a.reserved[q];
+    f.pad_ = 0;
+    for (int k = 0; k < 6; k++) {
+        const zhsm_result b = res_b[6 * (size_t)r + k];
+        f.n_loops++;
+        for (int q = 0; q < 4; q++) f.diag[q] += b.reserved[q];
+        if (b.valid != 1) break;  // a failing restart ends the restart loop
+        f.iterations += b.iterations;
+        if (b.error < f.error) {
+            f.error = b.error;
+            for (int q = 0; q < 3; q++) f.x[q] = b.x[q];
+        }
+    }
+    fin[r] = f;
+}
+
+// one pass of the PL-ICP kernel over `count` jobs in launches of at most `chunk`
+static cudaError_t plicp_pass(zhsm_handle *h, const PlicpArgs &a, int count, int chunk, int n, cudaStream_t st, int *launched) {
+    for (int off = 0; off < count; off += chunk) {
+        PlicpArgs c = a;
+        c.B = count - off < chunk ? count - off : chunk;
+        c.ref_idx = a.ref_idx + off;
+        c.sens_idx = a.sens_idx + off;
+        if (a.first_guess) c.first_guess = a.first_guess + 3 * (size_t)off;
+        if (a.fin) c.fin = a.fin + off;
+        if (a.out_idx) c.out_idx = a.out_idx + off;  // (records and correspondences are addressed through it)
+        else {
+            c.results = a.results + off;
+            if (a.corr_j1) { c.corr_j1 = a.corr_j1 + (size_t)off * n; c.corr_j2 = a.corr_j2 + (size_t)off * n; }
+        }
+        cudaError_t e = plicp_launch(c, h->sm_count, st, launched);
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
+// `a` is ready for an ordinary pass over a.B jobs (everything on the device).  Blocks until pass A is done (the number
+// of restarting jobs is needed on the host).
+static zhsm_status plicp_fanout(zhsm_handle *h, const PlicpArgs &a, int chunk, cudaStream_t st, int *launched) {
+    const int B = a.B, n = a.L.n;
+    void *p;
+    zhsm_status s;
+    if ((s = zhsm_stage(h, 24, sizeof(int32_t) * (3 * (size_t)B + 4), &p)) != ZHSM_OK) return s;
+    int32_t *count = (int32_t *)p, *list = count + 4, *ref_f = list + B, *sens_f = ref_f + B;
+    ZHSM_CUDA_TRY(h, cudaMemsetAsync(count, 0, sizeof(int32_t), st));
+    PlicpArgs A = a;
+    A.P.restart = 0;
+    ZHSM_CUDA_TRY(h, plicp_pass(h, A, B, chunk, n, st, launched));
+    restart_select_kernel<<<(B + 255) / 256, 256, 0, st>>>(a.results, a.ref_idx, a.sens_idx, B, a.P.restart_threshold_mean_error, list,
+                                                          ref_f, sens_f, count);
+    ZHSM_CUDA_TRY(h, cudaGetLastError());
+    int32_t R = 0;
+    ZHSM_CUDA_TRY(h, cudaMemcpyAsync(&R, count, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    ZHSM_CUDA_TRY(h, cudaStreamSynchronize(st));
+    *launched += 1;
+    if (R <= 0) return ZHSM_OK;
+    const size_t R6 = 6 * (size_t)R;
+    if ((s = zhsm_stage(h, 25, (sizeof(int32_t) * 2 + sizeof(double) * 3) * R6 + 64, &p)) != ZHSM_OK) return s;
+    double *guess_b = (double *)p;
+    int32_t *ref_b = (int32_t *)(guess_b + 3 * R6), *sens_b = ref_b + R6;
+    if ((s = zhsm_stage(h, 26, sizeof(zhsm_result) * R6, &p)) != ZHSM_OK) return s;
+    zhsm_result *res_b = (zhsm_result *)p;
+    if ((s = zhsm_stage(h, 27, sizeof(PlicpFin) * (size_t)R, &p)) != ZHSM_OK) return s;
+    PlicpFin *fin = (PlicpFin *)p;
+    restart_jobs_kernel<<<(int)((R6 + 255) / 256), 256, 0, st>>>(a.results, ref_f, sens_f, list, R, a.P.restart_dt,
+                                                                a.P.restart_dtheta, ref_b, sens_b, guess_b);
+    ZHSM_CUDA_TRY(h, cudaGetLastError());
+    PlicpArgs Bq = a;
+    Bq.P.restart = 0;
+    Bq.P.do_compute_covariance = 0;
+    Bq.ref_idx = ref_b; Bq.sens_idx = sens_b; Bq.first_guess = guess_b;
+    Bq.results = res_b; Bq.corr_j1 = nullptr; Bq.corr_j2 = nullptr;
+    ZHSM_CUDA_TRY(h, plicp_pass(h, Bq, (int)R6, chunk, n, st, launched));
+    restart_combine_kernel<<<(R + 255) / 256, 256, 0, st>>>(a.results, res_b, list, R, fin);
+    ZHSM_CUDA_TRY(h, cudaGetLastError());
+    PlicpArgs Cq = a;
+    Cq.ref_idx = ref_f; Cq.sens_idx = sens_f; Cq.first_guess = nullptr;
+    Cq.fin = fin; Cq.out_idx = list;
+    ZHSM_CUDA_TRY(h, plicp_pass(h, Cq, R, chunk, n, st, launched));
+    *launched += 2;
+    return ZHSM_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // batched PL-ICP
 // ---------------------------------------------------------------------------------------------------------
 extern "C" zhsm_status zhsm_plicp_batch(zhsm_handle *h, const float *scans, int S, const int32_t *ref_idx,
@@ -420,15 +557,10 @@ extern "C" zhsm_status zhsm_plicp_batch(zhsm_handle *h, const float *scans, int 
     a.owner = (const int32_t *)p;
     ZHSM_CUDA_TRY(h, cudaEventRecord(h->ev0, st));
     int launched = 0;
-    for (int off = 0; off < B; off += chunk) {
-        PlicpArgs c = a;
-        c.B = B - off < chunk ? B - off : chunk;
-        c.ref_idx = a.ref_idx + off;
-        c.sens_idx = a.sens_idx + off;
-        if (a.first_guess) c.first_guess = a.first_guess + 3 * (size_t)off;
-        c.results = a.results + off;
-        if (a.corr_j1) { c.corr_j1 = a.corr_j1 + (size_t)off * n; c.corr_j2 = a.corr_j2 + (size_t)off * n; }
-        ZHSM_CUDA_TRY(h, plicp_launch(c, h->sm_count, st, &launched));
+    if (P.restart && B <= h->knob_fanout && a.ns != 4) {
+        if ((s = plicp_fanout(h, a, chunk, st, &launched)) != ZHSM_OK) return s;
+    } else {
+        ZHSM_CUDA_TRY(h, plicp_pass(h, a, B, chunk, n, st, &launched));
     }
     h->launches += launched;
     ZHSM_CUDA_TRY(h, cudaEventRecord(h->ev1, st));

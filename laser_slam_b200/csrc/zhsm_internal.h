@@ -10,7 +10,7 @@
 
 #define ZHSM_MAX_BEAMS 4096
 #define ZHSM_MAX_ITER 64
-#define ZHSM_STAGE_SLOTS 24
+#define ZHSM_STAGE_SLOTS 28
 
 struct zhsm_handle {
     int device = 0;
@@ -29,6 +29,7 @@ struct zhsm_handle {
     int knob_chunk = 131072;   // ZHSM_PLICP_CHUNK: jobs per launch (bounds the jump-table scratch)
     int knob_chunk_iters = -1; // ZHSM_PLICP_CHUNK_ITERS: first iterations searched in chunk order; -1: by CTA shape (plicp_chunk_iters)
     int knob_smem_pad = 0;     // ZHSM_PLICP_SMEM_PAD: extra dynamic shared memory (fewer CTAs per SM)
+    int knob_fanout = 1 << 30; // ZHSM_PLICP_FANOUT: batches of up to this many jobs run sm_icp's restarts as a second batch (0: never)
     int knob_pool = 1;         // ZHSM_PLICP_POOL=0: the 256-thread shape runs its instance without the walk pool (plicp2_t256r.cu; tests)
     int hash_T = 0, hash_C = 0;  // CTA shape the hash matrices were built for (zhsm_set_laser)
     uint32_t *d_hashmat_ms = nullptr;  // the same for the multi-start instance's shape (128 threads per job)
@@ -70,6 +71,17 @@ struct LaserDev {
     int flags;  // ZHSM_LASER_*
 };
 
+// sm_icp's restart loop as a second batch (zhsm_api.cu: plicp_fanout): what the LAST pass of a restarted job starts from
+struct PlicpFin {
+    double x[3];        // best pose over loop 0 and the restarts
+    double error;       // its total error
+    int32_t nvalid;     // loop 0's correspondences (sm_result.nvalid)
+    int32_t iterations; // summed over the loops that count
+    int32_t n_loops;    // icp_loop executions
+    int32_t diag[4];    // walks, first-pass walks, verify rounds, walk steps of the passes before (zhsm_result.reserved)
+    int32_t pad_;
+};
+
 struct PlicpArgs {
     const float *scans;      // [S][n]
     const int32_t *ref_idx;  // [B]
@@ -89,6 +101,9 @@ struct PlicpArgs {
     int hash_chunk;          // stream elements hashed per thread (even)
     int chunk_iters;         // first iterations of an icp_loop searched in chunk order (find_correspondences)
     int pool;                // 0: the 256-thread shape is launched from plicp2_t256r.cu (no walk pool); tests only
+    const PlicpFin *fin;     // not null: the jobs skip the icp_loops and run the final stage only (correspondences at the
+                             // given pose, hash, covariance, record) with this bookkeeping -- the last pass of plicp_fanout
+    const int32_t *out_idx;  // not null: job k writes record (and correspondences) out_idx[k] instead of k
     int B;
     LaserDev L;
     zhsm_plicp_params P;

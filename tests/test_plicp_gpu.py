@@ -378,6 +378,47 @@ def test_walk_pool_same_bytes_as_ray_by_ray():
     assert np.array_equal(a.tobytes(), b.tobytes())
 
 
+@pytest.mark.parametrize("log", ["intel-lab", "fr079"])
+def test_restarts_as_second_batch_same_bytes(log):
+    """sm_icp's restart loop (six perturbed icp_loops, one after the other) runs as a second batch of one-loop jobs for
+    small batches (zhsm_api.cu: plicp_fanout; ZHSM_PLICP_FANOUT is the largest such batch, 0 = always in the job).  Each
+    loop depends on its start pose only, so the records must be the same BYTES either way -- pose, error, iterations,
+    n_loops, nvalid, hash, every correspondence (diagnostics aside; covariance to 1e-6: shared-memory atomics) -- on
+    real logs, where 10 % (intel-lab) to 40 % (fr079) of the pairs restart."""
+    import os
+    import laser_slam_b200 as zh
+    g = load_log(log)
+    out = {}
+    old = os.environ.get("ZHSM_PLICP_FANOUT")
+    try:
+        for fan in ("100000", "0"):
+            os.environ["ZHSM_PLICP_FANOUT"] = fan
+            eng = zh.Engine(0)
+            try:
+                eng.set_laser(make_laser(g))
+                scans = eng.median_filter(g["scans"].copy())
+                S = scans.shape[0]
+                p = eng.default_plicp_params()
+                p.do_compute_covariance = 1
+                out[fan] = eng.plicp(scans, np.arange(S - 1), np.arange(1, S), params=p, want_corr=True)
+            finally:
+                eng.close()
+    finally:
+        if old is None:
+            os.environ.pop("ZHSM_PLICP_FANOUT", None)
+        else:
+            os.environ["ZHSM_PLICP_FANOUT"] = old
+    (a, a1, a2), (b, b1, b2) = out["100000"], out["0"]
+    restarted = b["n_loops"] > 1
+    assert 0.05 < restarted.mean() < 0.6, restarted.mean()
+    assert np.array_equal(a1, b1) and np.array_equal(a2, b2)
+    a, b = a.copy(), b.copy()
+    assert np.allclose(a["cov"], b["cov"], rtol=1e-6, atol=1e-15)
+    a["cov"] = b["cov"]; a["reserved"] = b["reserved"]
+    bad = np.flatnonzero([x.tobytes() != y.tobytes() for x, y in zip(a, b)])
+    assert bad.size == 0, (bad[:10], a[bad[:3]], b[bad[:3]])
+
+
 def _same_records(a, b, with_cov):
     """Two CTA shapes of the kernel on the same jobs: every integer of the record equal (valid, status, iterations, nvalid,
     correspondence hash, loops), pose and error equal to rounding (the 14 GPC sums are added in a tree whose shape follows
