@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libzhsm.so")
-SOURCES = ["zhsm_api.cu", "plicp2_dispatch.cu", "plicp2_t64.cu", "plicp2_t128.cu", "plicp2_t160.cu", "plicp2_t192.cu", "plicp2_t256.cu", "plicp2_t256r.cu", "plicp2_t512.cu", "plicp2_jump.cu", "plicp2_debug.cu", "psm_sm100.cu", "zhsm_psm_api.cu", "icp_sm100.cu", "zhsm_icp_api.cu", "graph_sm100.cu", "submap_sm100.cu", "synth_sm100.cu", "csm_compat.cu", "zhsm_noalloc.cu", "zhsm_handoff.cu", "zhsm_group.cu", "plicp2_ms128.cu"]
+SOURCES = ["zhsm_api.cu", "plicp2_dispatch.cu", "plicp2_t64.cu", "plicp2_t128.cu", "plicp2_t160.cu", "plicp2_t192.cu", "plicp2_t256.cu", "plicp2_t256r.cu", "plicp2_t512.cu", "plicp2_final.cu", "plicp2_jump.cu", "plicp2_debug.cu", "psm_sm100.cu", "zhsm_psm_api.cu", "icp_sm100.cu", "zhsm_icp_api.cu", "graph_sm100.cu", "submap_sm100.cu", "synth_sm100.cu", "csm_compat.cu", "zhsm_noalloc.cu", "zhsm_handoff.cu", "zhsm_group.cu", "plicp2_ms128.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 # -fmad=false: the reference links an x86-64 (no FMA contraction) CSM; every a*b+c must round twice like it does
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-fmad=false",

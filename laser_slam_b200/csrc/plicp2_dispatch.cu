@@ -11,6 +11,7 @@ cudaError_t plicp_launch_t192(const PlicpArgs &a, cudaStream_t st);
 cudaError_t plicp_launch_t256(const PlicpArgs &a, cudaStream_t st);
 cudaError_t plicp_launch_t512(const PlicpArgs &a, cudaStream_t st);
 cudaError_t plicp_launch_t256_ray(const PlicpArgs &a, cudaStream_t st);
+cudaError_t plicp_launch_final(const PlicpArgs &a, cudaStream_t st);
 cudaError_t plicp_launch_ms128(const PlicpArgs &a, cudaStream_t st);
 
 // CTA size per beam count.  What counts is jobs per SM (the shared-memory footprint, ~51 B per beam, decides: 4 at 1080
@@ -84,7 +85,8 @@ cudaError_t plicp_launch(const PlicpArgs &a, int sm_count, cudaStream_t st, int 
         if (e == cudaSuccess && launched) *launched += 1;
         return e;
     }
-    if (T == 256 && !a.pool) e = plicp_launch_t256_ray(a, st);  // tests: the 256-thread shape without the walk pool
+    if (a.fin) e = plicp_launch_final(a, st);  // the final-only pass of plicp_fanout (plicp2_final.cu)
+    else if (T == 256 && !a.pool) e = plicp_launch_t256_ray(a, st);  // tests: the 256-thread shape without the walk pool
     else
     e = T == 64 ? plicp_launch_t64(a, st) : T == 128 ? plicp_launch_t128(a, st) : T == 160 ? plicp_launch_t160(a, st) : T == 192 ? plicp_launch_t192(a, st) : T == 256 ? plicp_launch_t256(a, st) : plicp_launch_t512(a, st);
     if (e == cudaSuccess && launched) *launched += 1;

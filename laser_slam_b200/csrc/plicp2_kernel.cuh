@@ -22,6 +22,14 @@ constexpr bool kList = T >= PLICP_LIST_MIN_T;
 #ifndef PLICP_FLAT
 #define PLICP_FLAT 1
 #endif
+// The final-only instances (plicp2_final.cu): the last pass of a job whose restarts ran as a second batch
+// (zhsm_api.cu: plicp_fanout).  A compile-time mode, so that the ordinary instances carry nothing of it.
+#ifndef PLICP_FINAL
+#define PLICP_FINAL 0
+#endif
+#ifndef PLICP_MAX_LOOPS
+#define PLICP_MAX_LOOPS 7   // icp_loops a job may run: 1 + sm_icp's six restarts (tuning builds: 1 = no in-job restarts)
+#endif
 #ifndef PLICP_FLAT_ALL
 #define PLICP_FLAT_ALL 0   // tuning builds: the short-scan instances as well (no list there: every walk ends in its lane)
 #endif
@@ -390,7 +398,7 @@ plicp2_kernel(PlicpArgs a, const Lay lay0) {
     }
     if (bad_job) {
         // device-resident job lists are not checked by the host: a bad index fails its own job, never the batch
-        const int ob = a.out_idx ? a.out_idx[job] : job;
+        const int ob = PLICP_FINAL ? a.out_idx[job] : job;
         if (t == 0) {
             zhsm_result r = {};
             r.status = ZHSM_JOB_INVALID_SCAN;
@@ -458,7 +466,7 @@ plicp2_kernel(PlicpArgs a, const Lay lay0) {
     const int tot = block_sum<T>((nvf_ref << 16) | nvf_sens, ctl->ired, 0);
     const int tot_bad = pl_sync_or<T>(bad_field);
     const int tot_ref = tot >> 16, tot_sens = tot & 0xffff;
-    const int out = a.out_idx ? a.out_idx[job] : job;
+    const int out = PLICP_FINAL ? a.out_idx[job] : job;
     zhsm_result *res = a.results + out;
     int16_t *oj1 = a.corr_j1 ? a.corr_j1 + (size_t)out * n : nullptr;
     int16_t *oj2 = a.corr_j2 ? a.corr_j2 + (size_t)out * n : nullptr;
@@ -516,7 +524,7 @@ plicp2_kernel(PlicpArgs a, const Lay lay0) {
     int *st_ = st_arr;
 #endif
 
-    if (a.fin) {
+    if constexpr (PLICP_FINAL != 0) {
         // The last pass of a job whose restarts ran as a second batch (zhsm_api.cu: plicp_fanout): the bookkeeping of
         // sm_icp comes with the launch, what is left is "recompute correspondences in case of restarts" and the record.
         if (t == 0) {
@@ -535,8 +543,7 @@ plicp2_kernel(PlicpArgs a, const Lay lay0) {
     }
     // (the compiler unrolls this loop of 7: 600 KB of code, and 3.4 % FASTER on the 1080-beam batch than with
     // `#pragma unroll 1` -- the first copy, the only one most jobs run, is specialised for loop == 0; measured r02p)
-    if (!a.fin)
-    for (int loop = 0; loop < 7; loop++) {
+    for (int loop = 0; loop < (PLICP_FINAL ? 0 : PLICP_MAX_LOOPS); loop++) {
         int iteration = 0, all_ok = 1, par = 0, newest = 0;
         for (iteration = 0; iteration < max_it; iteration++) {
             it.x0 = ctl->x[par][0];
@@ -778,7 +785,7 @@ plicp2_kernel(PlicpArgs a, const Lay lay0) {
                         best_error = loop_error;
                         for (int k = 0; k < 3; k++) best_x[k] = ctl->x[newest][k];
                     }
-                    next = loop < 6;
+                    next = loop < PLICP_MAX_LOOPS - 1;
                 }
             }
             if (next) {
