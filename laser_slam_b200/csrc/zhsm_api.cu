@@ -107,7 +107,9 @@ extern "C" zhsm_status zhsm_create(int device, zhsm_handle **out) {
     h->sm_count = prop.multiProcessorCount;
     if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreate(&h->ev0) != cudaSuccess || cudaEventCreate(&h->ev1) != cudaSuccess ||
-        cudaEventCreateWithFlags(&h->ev_busy, cudaEventDisableTiming) != cudaSuccess) {
+        cudaEventCreateWithFlags(&h->ev_busy, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&h->ev_stat, cudaEventDisableTiming) != cudaSuccess ||
+        cudaMallocHost(&h->stat_pin, sizeof(int32_t)) != cudaSuccess || cudaMalloc(&h->d_stat, sizeof(int32_t)) != cudaSuccess) {
         zhsm_destroy(h);
         return ZHSM_ERR_CUDA;
     }
@@ -136,6 +138,9 @@ extern "C" void zhsm_destroy(zhsm_handle *h) {
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     if (h->ev_busy) cudaEventDestroy(h->ev_busy);
+    if (h->ev_stat) cudaEventDestroy(h->ev_stat);
+    if (h->stat_pin) cudaFreeHost(h->stat_pin);
+    if (h->d_stat) cudaFree(h->d_stat);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -373,6 +378,39 @@ static __global__ void restart_combine_kernel(const zhsm_result *res, const zhsm
     fin[r] = f;
 }
 
+static __global__ void restart_count_kernel(const zhsm_result *res, int B, int32_t *count) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool r = j < B && res[j].n_loops > 1;
+    const unsigned m = __ballot_sync(0xffffffffu, r);
+    if ((threadIdx.x & 31) == 0 && m) atomicAdd(count, __popc(m));
+}
+
+// Fan out or restart in the job?  The fan-out costs two more passes (each ends with the tail of its last jobs) and a
+// round trip to the host: a few per cent of a mid-size batch that hardly restarts (the synthetic pairs: 1 job in
+// 20 000; 16.4 -> 17.0 ms per 20k pairs, and 7 % of the two-handle end-to-end rate, whose chunks overlap) and 1.6x the
+// rate of one that does (the logs: 10-50 % of the pairs).  So: small batches always (a batch of one behind sm_icp() is
+// 7 loops against 3 passes when it restarts, a 30 us round trip when not), otherwise by what the handle's previous
+// batch did.
+static bool plicp_use_fanout(zhsm_handle *h, const zhsm_plicp_params &P, int B, int ns) {
+    if (h->stat_pending && cudaEventQuery(h->ev_stat) == cudaSuccess) {
+        h->restart_frac = h->stat_B > 0 ? (float)*h->stat_pin / (float)h->stat_B : 0.f;
+        h->stat_pending = false;
+    } else if (h->stat_pending) cudaGetLastError();  // (cudaErrorNotReady is not an error)
+    if (!P.restart || ns == 4 || B > h->knob_fanout) return false;
+    return B <= 4096 || h->restart_frac < 0.f || h->restart_frac >= 0.02f;
+}
+
+// after an in-job pass: count the restarted jobs, the number travels back behind the stream
+static void plicp_issue_restart_count(zhsm_handle *h, const zhsm_result *d_results, int B, cudaStream_t st) {
+    if (h->stat_pending) return;
+    if (cudaMemsetAsync(h->d_stat, 0, sizeof(int32_t), st) != cudaSuccess) { cudaGetLastError(); return; }
+    restart_count_kernel<<<(B + 255) / 256, 256, 0, st>>>(d_results, B, h->d_stat);
+    if (cudaMemcpyAsync(h->stat_pin, h->d_stat, sizeof(int32_t), cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+        cudaEventRecord(h->ev_stat, st) != cudaSuccess) { cudaGetLastError(); return; }
+    h->stat_B = B;
+    h->stat_pending = true;
+}
+
 // one pass of the PL-ICP kernel over `count` jobs in launches of at most `chunk`
 static cudaError_t plicp_pass(zhsm_handle *h, const PlicpArgs &a, int count, int chunk, int n, cudaStream_t st, int *launched) {
     for (int off = 0; off < count; off += chunk) {
@@ -412,6 +450,7 @@ static zhsm_status plicp_fanout(zhsm_handle *h, const PlicpArgs &a, int chunk, c
     ZHSM_CUDA_TRY(h, cudaMemcpyAsync(&R, count, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     ZHSM_CUDA_TRY(h, cudaStreamSynchronize(st));
     *launched += 1;
+    h->restart_frac = (float)R / (float)B;
     if (R <= 0) return ZHSM_OK;
     const size_t R6 = 6 * (size_t)R;
     if ((s = zhsm_stage(h, 25, (sizeof(int32_t) * 2 + sizeof(double) * 3) * R6 + 64, &p)) != ZHSM_OK) return s;
@@ -557,10 +596,11 @@ extern "C" zhsm_status zhsm_plicp_batch(zhsm_handle *h, const float *scans, int 
     a.owner = (const int32_t *)p;
     ZHSM_CUDA_TRY(h, cudaEventRecord(h->ev0, st));
     int launched = 0;
-    if (P.restart && B <= h->knob_fanout && a.ns != 4) {
+    if (plicp_use_fanout(h, P, B, a.ns)) {
         if ((s = plicp_fanout(h, a, chunk, st, &launched)) != ZHSM_OK) return s;
     } else {
         ZHSM_CUDA_TRY(h, plicp_pass(h, a, B, chunk, n, st, &launched));
+        if (P.restart) { plicp_issue_restart_count(h, a.results, B, st); launched++; }
     }
     h->launches += launched;
     ZHSM_CUDA_TRY(h, cudaEventRecord(h->ev1, st));

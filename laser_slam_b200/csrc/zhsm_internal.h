@@ -30,6 +30,15 @@ struct zhsm_handle {
     int knob_chunk_iters = -1; // ZHSM_PLICP_CHUNK_ITERS: first iterations searched in chunk order; -1: by CTA shape (plicp_chunk_iters)
     int knob_smem_pad = 0;     // ZHSM_PLICP_SMEM_PAD: extra dynamic shared memory (fewer CTAs per SM)
     int knob_fanout = 1 << 30; // ZHSM_PLICP_FANOUT: batches of up to this many jobs run sm_icp's restarts as a second batch (0: never)
+    // How often the last PL-ICP batch restarted (jobs with n_loops > 1 / jobs), -1: not known yet.  The fan-out measures
+    // it on the host; the in-job pass counts on the device and the number comes back asynchronously (pinned stat_pin,
+    // ev_stat) and is picked up by the next call.  See plicp_use_fanout (zhsm_api.cu).
+    float restart_frac = -1.f;
+    int32_t *stat_pin = nullptr;   // pinned: restarted jobs of the batch that issued the count
+    int32_t *d_stat = nullptr;     // its device counter
+    int stat_B = 0;                // that batch's size
+    cudaEvent_t ev_stat = nullptr;
+    bool stat_pending = false;
     int knob_pool = 1;         // ZHSM_PLICP_POOL=0: the 256-thread shape runs its instance without the walk pool (plicp2_t256r.cu; tests)
     int hash_T = 0, hash_C = 0;  // CTA shape the hash matrices were built for (zhsm_set_laser)
     uint32_t *d_hashmat_ms = nullptr;  // the same for the multi-start instance's shape (128 threads per job)

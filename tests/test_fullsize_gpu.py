@@ -19,8 +19,17 @@ from oracle import pyoracle as po
 pytestmark = pytest.mark.gpu
 
 
+def _rec(t):
+    """Records without their diagnostics (zhsm_result.reserved: walks, rounds, steps executed).  Those depend on how a
+    restarted job's loops were scheduled -- in the job, or as a second batch (zhsm_api.cu: plicp_fanout), which the
+    handle picks per call from what its previous batch did -- everything else must be the same bytes."""
+    r = (t.cpu().numpy() if hasattr(t, "cpu") else t).view(np.uint8).reshape(-1, 128).copy().view(zh.RESULT_DTYPE).reshape(-1)
+    r["reserved"] = 0
+    return r
+
+
 def _crc(t):
-    return zlib.crc32(t.cpu().numpy().tobytes())
+    return zlib.crc32(_rec(t).tobytes())
 
 
 def test_plicp_one_million_pairs(engine):
@@ -43,7 +52,7 @@ def test_plicp_one_million_pairs(engine):
     rp = ri[perm].contiguous()
     engine.plicp(scans, rp, rp + 1, results=res2)
     engine.sync()
-    assert torch.equal(res2, res1[perm])                              # independence of jobs
+    assert np.array_equal(_rec(res2).tobytes(), _rec(res1[perm]).tobytes())   # independence of jobs
     r = res1.cpu().numpy().view(zh.RESULT_DTYPE).reshape(-1)
     assert (r["valid"] == 1).mean() > 0.9999
     err = np.abs(r["x"] - truth.cpu().numpy())
@@ -54,7 +63,7 @@ def test_plicp_one_million_pairs(engine):
     K = 4096
     h = scans[: 2 * K].cpu().numpy()
     rh = engine.plicp(h, np.arange(0, 2 * K, 2), np.arange(1, 2 * K, 2))
-    assert np.array_equal(rh.view(np.uint8).reshape(K, 128), res1[:K].cpu().numpy())
+    assert np.array_equal(_rec(rh).tobytes(), _rec(res1[:K]).tobytes())
     # oracle on a sample spread over the batch
     idx = np.linspace(0, P - 1, 512).astype(np.int64)
     hs = torch.stack([scans[2 * idx], scans[2 * idx + 1]], 1).reshape(-1, n).cpu().numpy()
