@@ -136,7 +136,14 @@ zhsm_status zhsm_median_filter_batch(zhsm_handle *h, float *scans, int S, unsign
 /* Batched CCanonicalMatcher::FMatch(LDP,LDP) (ZHCanonical_Matcher.cpp:251-285): fromPMScan2LDP on both scans
  * (:193-227) + sm_icp (:274).  Scans must already be median filtered (the wrapper filters each scan once when
  * it arrives, :233-237).  first_guess may be NULL (= 0,0,0 as :270-272) or [B][3] doubles (m,m,rad).
- * corr_j1/corr_j2 may be NULL or [B][n] int16 (-1 = no correspondence). */
+ * corr_j1/corr_j2 may be NULL or [B][n] int16 (-1 = no correspondence).
+ * sm_icp's restart loop (params->restart: six perturbed icp_loops when the mean error is above
+ * restart_threshold_mean_error) runs either inside the job, one loop after the other, or as a second batch of one-loop
+ * jobs -- always for batches of up to 4096 jobs, otherwise when the handle's previous batch restarted on 2 % of its
+ * jobs or more.  Same records either way, up to the diagnostics in reserved[].  The second form needs the number of
+ * restarting jobs on the host: the call then BLOCKS until the first pass is done, also with the *_ON_DEVICE flags
+ * (what it queues after that is asynchronous as before; device-resident job arrays are not read after the call
+ * returns, the scan pool and the result buffers are, as ever, until the stream has run). */
 zhsm_status zhsm_plicp_batch(zhsm_handle *h, const float *scans, int S, const int32_t *ref_idx,
                              const int32_t *sens_idx, const double *first_guess, int B,
                              const zhsm_plicp_params *params, zhsm_result *results, int16_t *corr_j1,
