@@ -32,8 +32,9 @@ cudaError_t plicp_launch_ms128(const PlicpArgs &a, cudaStream_t st);
 // logs, whose jobs differ by an order of magnitude (sm_icp restarts on 10 % of intel-lab's pairs, 3.4-4 loops per pair
 // on fr079 / mit-cscail): log x 16 in one batch, k pairs/s, threads 64 / 128 / 192: intel-lab (181 beams) 921 / 970 /
 // 966, fr079 (361) 242 / 306 / 291, mit-cscail (361) 195 / 254 / 241; the log once: 380 / 454 / 472, 109 / 144 / 150,
-// 58 / 85 / 86 (profiles/r03d_logs_by_threads.txt).  A long job wants its threads; the instance stays selectable
-// (ZHSM_PLICP_T=64), off.
+// 58 / 85 / 86 (profiles/r03d_logs_by_threads.txt).  A long job wants its threads.  With the restarts as a second
+// batch (zhsm_api.cu: plicp_fanout) the logs' jobs are one-loop jobs too, and the 64-thread shape is used for short scans
+// in LARGE batches (plicp_wide_batch_T, zhsm_internal.h); the handle's shape stays 128 threads.
 #ifndef PLICP_T64_MAX_BEAMS
 #define PLICP_T64_MAX_BEAMS 0   // (off: see above)
 #endif

@@ -1,6 +1,6 @@
 // laser_slam_b200/csrc/plicp2_t64.cu -- PL-ICP kernel instance with 64-thread CTAs (one CTA per scan pair): eight
-// resident CTAs per SM at 128 registers.  Tuning only (ZHSM_PLICP_T=64): faster on uniform batches of short scans, slower
-// on the real logs (plicp2_dispatch.cu).
+// resident CTAs per SM at 128 registers.  Short scans (up to 256 beams) in large batches (plicp_wide_batch_T,
+// zhsm_internal.h); a few waves of jobs are faster with 128 threads each.
 #include "plicp2_kernel.cuh"
 #include "plicp2_launch.cuh"
 

@@ -135,6 +135,7 @@ extern "C" void zhsm_destroy(zhsm_handle *h) {
     if (h->d_cs) cudaFree(h->d_cs);
     if (h->d_hashmat) cudaFree(h->d_hashmat);
     if (h->d_hashmat_ms) cudaFree(h->d_hashmat_ms);
+    if (h->d_hashmat_64) cudaFree(h->d_hashmat_64);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     if (h->ev_busy) cudaEventDestroy(h->ev_busy);
@@ -220,6 +221,16 @@ extern "C" zhsm_status zhsm_set_laser(zhsm_handle *h, const zhsm_laser *laser) {
         ZHSM_CUDA_TRY(h, cudaMalloc(&h->d_hashmat_ms, sizeof(uint32_t) * mat.size()));
         ZHSM_CUDA_TRY(h, cudaMemcpy(h->d_hashmat_ms, mat.data(), sizeof(uint32_t) * mat.size(), cudaMemcpyHostToDevice));
         h->hash_chunk_ms = ch_ms;
+        // ... and for the 64-thread shape of short scans (plicp_wide_batch_T)
+        if (h->d_hashmat_64) { cudaFree(h->d_hashmat_64); h->d_hashmat_64 = nullptr; }
+        if (n <= 256) {
+            int ch_64 = (n + 63) / 64;
+            if (ch_64 & 1) ch_64++;
+            plicp_build_hash_matrices(n, 64, ch_64, mat);
+            ZHSM_CUDA_TRY(h, cudaMalloc(&h->d_hashmat_64, sizeof(uint32_t) * mat.size()));
+            ZHSM_CUDA_TRY(h, cudaMemcpy(h->d_hashmat_64, mat.data(), sizeof(uint32_t) * mat.size(), cudaMemcpyHostToDevice));
+            h->hash_chunk_64 = ch_64;
+        }
     }
     h->laser = *laser;
     h->have_laser = true;
@@ -521,6 +532,12 @@ extern "C" zhsm_status zhsm_plicp_batch(zhsm_handle *h, const float *scans, int 
     a.hash_chunk = h->hash_chunk;
     a.chunk_iters = plicp_chunk_iters(h->knob_chunk_iters, h->hash_T);
     a.pool = h->knob_pool;
+    if (plicp_wide_batch_T(n, B, h->knob_T) == 64 && h->d_hashmat_64) {
+        a.T = 64;
+        a.hashmat = h->d_hashmat_64;
+        a.hash_chunk = h->hash_chunk_64;
+        a.chunk_iters = plicp_chunk_iters(h->knob_chunk_iters, 64);
+    }
     // ZHSM_MULTISTART: the caller promises jobs in runs of four that share both scans (pair-major multi-start).  Used
     // where it pays: long scans, whose single-job CTAs fit only twice per SM.  The kernel re-checks the promise per job.
     if ((flags & ZHSM_MULTISTART) && B % 4 == 0 && n > 1472 && plicp_ms128_smem_bytes(n) <= 227 * 1024 && (n + 127) / 128 <= 32 &&

@@ -43,6 +43,8 @@ struct zhsm_handle {
     int hash_T = 0, hash_C = 0;  // CTA shape the hash matrices were built for (zhsm_set_laser)
     uint32_t *d_hashmat_ms = nullptr;  // the same for the multi-start instance's shape (128 threads per job)
     int hash_chunk_ms = 0;
+    uint32_t *d_hashmat_64 = nullptr;  // ... and for the 64-thread shape (short scans in large batches: plicp_wide_batch_T)
+    int hash_chunk_64 = 0;
 
     bool have_laser = false;
     zhsm_laser laser{};
@@ -160,6 +162,12 @@ cudaError_t plicp_launch(const PlicpArgs &a, int sm_count, cudaStream_t st, int 
 // threads (long walks go to the list): 0: 87.3 k, 2: 84.4 k, 6: 77.1 k matches/s.
 // (the instances that run their walks as a pool, T >= 256, ignore the value: they have no chunk order)
 inline int plicp_chunk_iters(int knob, int T) { return knob >= 0 ? knob : (T >= 256 ? 0 : 2); }
+// Short scans in LARGE batches run 64 threads per job (8 jobs per SM instead of 4): measured on one B200
+// (profiles/r03c_cta_shapes.txt, r03s_logs_by_threads_fanout.txt), 64 against 128 threads: uniform batches of 60-80 k
+// pairs +17 % at 181 beams, +19 % at 256, +9 % at 361; intel-lab x 16 (42 736 jobs, restarts as a second batch) 1.93 M
+// against 1.58 M pairs/s, fr079 x 16 +8 %, mit-cscail x 16 -2 %; the logs ONCE (1-3 k jobs: a few waves, where a job's
+// own speed counts) 7-27 % slower.  0: the handle's shape.
+inline int plicp_wide_batch_T(int n, int B, int knob_T) { return (knob_T == 0 && n <= 256 && B >= 16384) ? 64 : 0; }
 size_t plicp_ms128_smem_bytes(int n);  // dynamic shared memory of the multi-start instance (4 jobs per CTA)
 size_t plicp_jump_bytes_per_job(int n);
 // CTA shape the PL-ICP kernel uses for n beams: T threads, C rays per thread, hash chunk (even) per thread
