@@ -333,7 +333,7 @@ def measure_c1(zh, eng, dev, stream, peaks, args):
            "iterations_per_pair": float(one["iterations"].mean()), "icp_loops_per_pair": float(one["n_loops"].mean()),
            "pairs_restarted_frac": float((one["n_loops"] > 1).mean()), "valid_frac": float((one["valid"] == 1).mean()),
            "roofline": roofline_block(flops, {**det, "iterations_per_pair": float(one["iterations"].mean())}, kern_ms,
-                                      peaks[64], "fp64_cuda_core", "plicp2_kernel<128> + jump_tables_kernel", ex),
+                                      peaks[64], "fp64_cuda_core", "plicp2_kernel<64> (short scans in a batch of 16 384 jobs or more; <128> for the log once) + jump_tables_kernel, restarts as a second batch", ex),
            "e2e": {"value": B / e2e_dt, "unit": UNIT, "steps": args.e2e_steps,
                    "h2d_bytes_per_step": int(raw_h.nbytes + 2 * B * 4), "d2h_bytes_per_step": int(B * 128),
                    "api": "zhsm_plicp_batch(host scans, host job lists, host records, ZHSM_FILTER_SCANS); pageable host "
