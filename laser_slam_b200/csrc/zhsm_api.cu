@@ -389,6 +389,9 @@ static __global__ void restart_combine_kernel(const zhsm_result *res, const zhsm
     fin[r] = f;
 }
 
+#ifndef ZHSM_FANOUT_MIN_FRAC
+#define ZHSM_FANOUT_MIN_FRAC 0.02f   // restarting share of the previous batch from which a larger batch fans out (tuning builds)
+#endif
 static __global__ void restart_count_kernel(const zhsm_result *res, int B, int32_t *count) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     const bool r = j < B && res[j].n_loops > 1;
@@ -408,7 +411,7 @@ static bool plicp_use_fanout(zhsm_handle *h, const zhsm_plicp_params &P, int B, 
         h->stat_pending = false;
     } else if (h->stat_pending) cudaGetLastError();  // (cudaErrorNotReady is not an error)
     if (!P.restart || ns == 4 || B > h->knob_fanout) return false;
-    return B <= 4096 || h->restart_frac < 0.f || h->restart_frac >= 0.02f;
+    return B <= 4096 || h->restart_frac < 0.f || h->restart_frac >= ZHSM_FANOUT_MIN_FRAC;
 }
 
 // after an in-job pass: count the restarted jobs, the number travels back behind the stream
