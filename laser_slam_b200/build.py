@@ -25,7 +25,7 @@ def build(force=False, verbose=False, variant=None, defs=()):
     OUT = os.path.join(HERE, "libzhsm%s.so" % ("_" + variant if variant else ""))
     extra = ["-D" + d for d in defs]
     os.makedirs(objdir, exist_ok=True)
-    headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))]
+    headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh", ".inc"))]
     headers.append(os.path.join(HERE, "..", "include", "zhsm.h"))
     headers.append(os.path.join(HERE, "..", "include", "csm_compat.h"))
     ccbin = [] if not os.path.exists("/usr/bin/g++") else ["-ccbin", "/usr/bin/g++"]
