@@ -139,8 +139,8 @@ zhsm_status zhsm_median_filter_batch(zhsm_handle *h, float *scans, int S, unsign
  * corr_j1/corr_j2 may be NULL or [B][n] int16 (-1 = no correspondence).
  * sm_icp's restart loop (params->restart: six perturbed icp_loops when the mean error is above
  * restart_threshold_mean_error) runs either inside the job, one loop after the other, or as a second batch of one-loop
- * jobs -- always for batches of up to 4096 jobs, otherwise when the handle's previous batch restarted on 2 % of its
- * jobs or more.  Same records either way, up to the diagnostics in reserved[].  The second form needs the number of
+ * jobs -- always for batches of 512 to 4096 jobs, for larger ones when the handle's previous batch restarted on 2 % of
+ * its jobs or more, never for smaller ones.  Same records either way, up to the diagnostics in reserved[].  The second form needs the number of
  * restarting jobs on the host: the call then BLOCKS until the first pass is done, also with the *_ON_DEVICE flags
  * (what it queues after that is asynchronous as before; device-resident job arrays are not read after the call
  * returns, the scan pool and the result buffers are, as ever, until the stream has run). */

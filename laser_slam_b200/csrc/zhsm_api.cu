@@ -402,15 +402,18 @@ static __global__ void restart_count_kernel(const zhsm_result *res, int B, int32
 // Fan out or restart in the job?  The fan-out costs two more passes (each ends with the tail of its last jobs) and a
 // round trip to the host: a few per cent of a mid-size batch that hardly restarts (the synthetic pairs: 1 job in
 // 20 000; 16.4 -> 17.0 ms per 20k pairs, and 7 % of the two-handle end-to-end rate, whose chunks overlap) and 1.6x the
-// rate of one that does (the logs: 10-50 % of the pairs).  So: small batches always (a batch of one behind sm_icp() is
-// 7 loops against 3 passes when it restarts, a 30 us round trip when not), otherwise by what the handle's previous
-// batch did.
+// rate of one that does (the logs: 10-50 % of the pairs).  So: batches of 512 to 4096 jobs always (a log run once: the
+// seven-loop jobs are its tail), larger ones by what the handle's previous batch did, and less than a wave of jobs
+// never: there every job runs at once anyway and three passes cost more launch latency than six loops take (a batch
+// of one behind sm_icp(), intel-lab, host buffers: 187 us without a restart, 947 us with one in the job, 1122 us as
+// three passes; tools/gpu_probe_latency.py).
 static bool plicp_use_fanout(zhsm_handle *h, const zhsm_plicp_params &P, int B, int ns) {
     if (h->stat_pending && cudaEventQuery(h->ev_stat) == cudaSuccess) {
         h->restart_frac = h->stat_B > 0 ? (float)*h->stat_pin / (float)h->stat_B : 0.f;
         h->stat_pending = false;
     } else if (h->stat_pending) cudaGetLastError();  // (cudaErrorNotReady is not an error)
     if (!P.restart || ns == 4 || B > h->knob_fanout) return false;
+    if (B < 512) return false;  // less than a wave of jobs: the passes' launch latencies outweigh six loops in a row
     return B <= 4096 || h->restart_frac < 0.f || h->restart_frac >= ZHSM_FANOUT_MIN_FRAC;
 }
 
