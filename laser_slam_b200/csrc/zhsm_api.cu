@@ -623,7 +623,7 @@ extern "C" zhsm_status zhsm_plicp_batch(zhsm_handle *h, const float *scans, int 
         if ((s = plicp_fanout(h, a, chunk, st, &launched)) != ZHSM_OK) return s;
     } else {
         ZHSM_CUDA_TRY(h, plicp_pass(h, a, B, chunk, n, st, &launched));
-        if (P.restart) { plicp_issue_restart_count(h, a.results, B, st); launched++; }
+        if (P.restart && B >= 512) { plicp_issue_restart_count(h, a.results, B, st); launched++; }  // (smaller batches never fan out)
     }
     h->launches += launched;
     ZHSM_CUDA_TRY(h, cudaEventRecord(h->ev1, st));
