@@ -234,6 +234,8 @@ extern "C" zhsm_status zhsm_set_laser(zhsm_handle *h, const zhsm_laser *laser) {
     }
     h->laser = *laser;
     h->have_laser = true;
+    h->restart_frac = -1.f;  // another sensor, another workload: what the previous batches did says nothing (plicp_use_fanout)
+    h->stat_pending = false;
     return ZHSM_OK;
 }
 
